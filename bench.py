@@ -1,0 +1,329 @@
+#!/usr/bin/env python
+"""bench.py — training samples/s of the data-parallel hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+One "step" = one minibatch step of the build-defined logistic regression (the slot of
+the reference's simulate_training, src/worker.cc:221-231) over B = 4096 rows of
+F = 1024 fp32 features per GPU — BASELINE.json config 3 at N = 1, config 4 at N > 1
+(one worker per GPU, gradients averaged every step).  Synthetic counter-based data
+(SURVEY.md §8d), generated on the device; the 4 GiB shard per GPU is far larger than
+L2 (126 MB), so consecutive steps never re-read cached rows.
+
+Prints ONE JSON line (rank 0).  Keys beyond the base contract:
+  roofline      achieved = algorithmic bytes per launch / CUDA-event time of the launch
+  cpu_baseline  the oracle's LR step (a port: the reference has no gradient step) on
+                one host thread — the reference runs one training thread per worker
+  e2e           the same metric through the C ABI with HOST buffers: per step one
+                minibatch is streamed from pinned host memory (sl_shard_*), one step is
+                taken and its loss is read back
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+F = 1024
+B = 4096
+ROWS_PER_GPU = 1 << 20
+ETA = 0.1
+METRIC = "training samples/sec"
+UNIT = "samples/s"
+
+
+def algorithmic_bytes_per_step(f=F, b=B) -> int:
+    # 4*(F+1) per sample (row + label) + 16*F per step (fp64 w read+write)
+    return 4 * (f + 1) * b + 16 * f
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic_per_step():
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        with open(p) as fh:
+            return float(json.load(fh)["dram_bytes_per_step"])
+    except Exception:
+        return None
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons = index, False, [], set()
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.dev = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def sample(self):
+        nv = self.nv
+        self.samples.append(nv.nvmlDeviceGetClockInfo(self.dev, nv.NVML_CLOCK_SM))
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev) if hasattr(
+            nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.dev)
+        names = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+                 0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown"}
+        for bit, n in names.items():
+            if r & bit:
+                self.reasons.add(n)
+
+    def run(self):
+        if self.nv is None:
+            return
+        while not self.stop_flag:
+            try:
+                self.sample()
+            except Exception:
+                break
+            time.sleep(0.002)
+
+    def result(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": []}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------------------
+def cpu_baseline_port(seconds: float = 8.0):
+    """Oracle LR step on ONE host thread (reference structure: one training thread per
+    worker, src/worker.cc:246), on a bounded sample of the config-3 workload."""
+    import oracle
+    orc = oracle.Oracle()
+    n = 1 << 15                       # 32768 rows x 1024 = 128 MiB: larger than host LLC
+    X, y = orc.synth(0, n, F)
+    w = np.zeros(F)
+    t0 = time.perf_counter()
+    orc.lr_steps(X, y, B, 0, 8, w, ETA)
+    per = (time.perf_counter() - t0) / 8
+    steps = int(max(8, min(4000, seconds / per)))
+    w[:] = 0
+    t0 = time.perf_counter()
+    orc.lr_steps(X, y, B, 0, steps, w, ETA)
+    dt = time.perf_counter() - t0
+    return {"value": steps * B / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{steps} steps of B={B} over a {n}x{F} fp32 shard, 1 thread, "
+                      f"{dt:.1f} s; oracle/sl_oracle_lr.c (the reference has no gradient step)",
+            "host_cores_online": orc.max_threads()}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU restatement with every host thread it can use — one
+    worker (thread) per core, each on its own shard slice, the reference's own
+    parallel structure (N worker processes, one training thread each)."""
+    if rank != 0:
+        return
+    import oracle
+    orc = oracle.Oracle()
+    W = orc.max_threads()
+    n = 1 << 14                                     # 64 MiB of rows per worker
+    shards = [orc.synth(k * n, n, F) for k in range(W)]
+    Xs, ys = [s[0] for s in shards], [s[1] for s in shards]
+    ws = [np.zeros(F) for _ in range(W)]
+    # a "step" here = one minibatch on every worker; bound the run to about a minute
+    t0 = time.perf_counter()
+    orc.lr_bench_workers(Xs, ys, B, 2, ws, ETA)
+    per = (time.perf_counter() - t0) / 2
+    budget = 60.0
+    steps = int(max(1, min(args.steps, budget / max(per, 1e-9))))
+    warm = int(max(1, min(args.warmup, 10.0 / max(per, 1e-9))))
+    orc.lr_bench_workers(Xs, ys, B, warm, ws, ETA)
+    dt = orc.lr_bench_workers(Xs, ys, B, steps, ws, ETA)
+    value = W * steps * B / dt
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "impl": "reference",
+        "config": {"workload": f"config 3 shape: F={F}, B={B} per worker, {W} CPU workers x "
+                               f"{n} rows (bounded sample)", "requested_steps": args.steps},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": W, "kind": "port",
+                         "sample": f"{steps} steps x {W} workers x B={B}; oracle port (the "
+                                   "reference's hot path does not compile and has no gradient "
+                                   "step, see DESIGN.md)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    from serverless_learn_b200 import Replica
+
+    torch.cuda.set_device(local_rank)
+    multi = world > 1
+    if multi:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if multi:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if not multi:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    r = Replica(F, B, eta=ETA, device=local_rank)
+    r.shard_synth(ROWS_PER_GPU, row0=rank * ROWS_PER_GPU)
+    if multi:
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(Replica.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        r.comm_init_rank(world, rank, bytes(uid.cpu().numpy().tobytes()))
+    step_fn = r.train_steps_sync if multi else r.train_steps
+
+    # ---- device-resident leg ("value") ------------------------------------------------
+    step_fn(args.warmup, want_loss=False)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    l0 = r.info("launches")
+    sampler.start()
+    t0 = time.perf_counter()
+    step_fn(args.steps, want_loss=False)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    sampler.stop_flag = True
+    dev_ms = r.last_train_ms()
+    launches = r.info("launches") - l0
+    barrier()
+    sampler.join(timeout=1.0)
+    dev_s = max_over_ranks(dev_ms * 1e-3)
+    wall_s = max_over_ranks(wall)
+    value = world * args.steps * B / dev_s
+
+    # ---- end-to-end leg: host buffers through the C ABI ---------------------------------
+    pool = 8
+    host = [torch.empty(B * (F + 1), dtype=torch.float32).pin_memory() for _ in range(pool)]
+    # host minibatches = the same synthetic rows, generated on the device by the product's
+    # own generator and read back once, outside any timed region
+    gen = Replica(F, B, eta=ETA, device=local_rank)
+    for i, hb in enumerate(host):
+        gen.shard_synth(B, row0=rank * ROWS_PER_GPU + i * B)
+        raw = gen.shard_read(0, gen.shard_bytes())
+        hb.copy_(torch.from_numpy(raw.view(np.float32)))
+    gen.close()
+    e2e_steps = int(min(args.steps, 512))
+    nbytes = B * (F + 1) * 4
+    e2e = Replica(F, B, eta=ETA, device=local_rank)
+    if multi:
+        uid2 = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid2.copy_(torch.frombuffer(bytearray(Replica.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid2, 0)
+        e2e.comm_init_rank(world, rank, bytes(uid2.cpu().numpy().tobytes()))
+    e2e_step = e2e.train_steps_sync if multi else e2e.train_steps
+
+    def one(i):
+        hb = host[i % pool]
+        e2e.shard_begin(nbytes)
+        e2e.shard_append_ptr(hb.data_ptr(), nbytes)
+        e2e.shard_end()
+        return e2e_step(1, want_loss=True)[0]
+
+    for i in range(max(3, min(args.warmup, 16))):
+        one(i)
+    barrier()
+    t0 = time.perf_counter()
+    loss = 0.0
+    for i in range(e2e_steps):
+        loss = one(i)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_value = world * e2e_steps * B / e2e_s
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        algo = algorithmic_bytes_per_step() * args.steps / max(launches, 1)
+        per_launch_s = dev_ms * 1e-3 / max(launches, 1)
+        achieved = algo / per_launch_s / 1e9
+        traffic = ncu_traffic_per_step()
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": ("config 3" if world == 1 else "config 4") +
+                                   f": logistic regression F={F}, B={B} per GPU, "
+                                   f"{ROWS_PER_GPU} rows x {F} fp32 resident per GPU",
+                       "l2": "inputs larger than L2 (4 GiB shard per GPU, sequential minibatches)",
+                       "parallelism": f"dp{world}" + (" (NCCL all-reduce of the gradient every step)" if multi else ""),
+                       "kernel_path": {1: "persistent", 2: "simple", 3: "simple+nccl"}.get(r.info("path"), "?"),
+                       "variant": r.info("variant"), "grid": r.info("grid"),
+                       "ring_slots": r.info("ring_slots")},
+            "wall_ms_per_step": 1e3 * wall_s / args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None if traffic is None else traffic * args.steps / max(launches, 1),
+                         "peak_source": peak_src,
+                         "algorithmic_bytes_per_step": algorithmic_bytes_per_step(),
+                         "kernel": "lr_persist_kernel" if r.info("path") == 1 else "lr_fwd+lr_grad+lr_finish",
+                         "launches": launches},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+                    "d2h_bytes_per_step": 8, "steps": e2e_steps, "last_loss": float(loss)},
+            "gpu_launches": int(launches),
+            "clocks": sampler.result(),
+        }
+        if world == 1:
+            line["cpu_baseline"] = cpu_baseline_port()
+        print(json.dumps(line), flush=True)
+    r.close()
+    e2e.close()
+    if multi:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4096)
+    ap.add_argument("--warmup", type=int, default=256)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        print(f"bench.py: --gpus {args.gpus} needs torchrun (WORLD_SIZE={world})", file=sys.stderr)
+        sys.exit(2)
+    run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

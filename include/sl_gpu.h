@@ -1,0 +1,134 @@
+/*
+ * sl_gpu.h — C ABI of the B200 (sm_100a) hot path of serverless_learn.
+ *
+ * The reference (sheaconlon/serverless_learn) has no plugin / FFI layer: its
+ * arithmetic sits inline in gRPC handlers and thread loops over file-scope
+ * globals.  Each entry point below replaces one of those inline loops; the
+ * comment on it cites the loop (file:line relative to the reference's root).
+ * The outer surface — roles, RPCs and messages of
+ * src/protos/serverless_learn.proto — is unchanged; INTEGRATION.md shows the
+ * edits a maintainer makes in master.cc / worker.cc / file_server.cc.
+ *
+ * Conventions
+ *   - plain C, opaque handle, plain pointers and sizes; no C++ or torch types.
+ *   - every function returns 0 on success and a negative SL_E* code on failure;
+ *     nothing throws across the boundary.  sl_last_error() gives the text.  The
+ *     reference's handlers always return Status::OK and report failure in the
+ *     ack's `ok` bool (src/master.cc:90,113; src/worker.cc:60,76,99): a shim maps
+ *     rc != 0 to ok=false.
+ *   - all `double*` / `void*` arguments are HOST pointers owned by the caller and
+ *     used only for the duration of the call (they match
+ *     RepeatedField<double>::data() / mutable_data() and Chunk::data()).
+ *   - one handle = one model replica (one worker, or the master) on one GPU.
+ *     Calls on one handle may come from any thread (the reference touches its
+ *     state from >=3 threads with no lock, src/worker.cc:242-246); they are
+ *     serialised on a per-handle mutex and one CUDA stream.
+ *   - there is no CPU fallback: without a usable CUDA device sl_create fails.
+ */
+#ifndef SL_GPU_H
+#define SL_GPU_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sl_handle sl_handle;
+
+enum {
+    SL_OK = 0,
+    SL_EINVAL = -1,   /* bad argument (length mismatch, shape not supported, ...) */
+    SL_ECUDA = -2,    /* a CUDA runtime call failed */
+    SL_ESTATE = -3,   /* call out of order (train before a shard is sealed, ...) */
+    SL_ENOMEM = -4,   /* host or device allocation failed */
+    SL_ETIMEOUT = -5, /* an in-kernel wait gave up (exchange watchdog) */
+    SL_ENCCL = -6     /* NCCL missing or a NCCL call failed */
+};
+
+/* ---- lifetime ----------------------------------------------------------------
+ * Replaces the file-scope state `model_state`, `old_state`, `LEARN_RATE`
+ * (src/master.cc:58-60; used but never declared in src/worker.cc).  D is the model
+ * length — the reference's vectors start empty and can never grow,
+ * so D is fixed here (repair R6).  F, B, eta configure the minibatch step; the
+ * model is bias-free logistic regression so D must equal F.  lambda is
+ * LEARN_RATE (0.5 in the reference).  Both vectors start at zero. */
+int sl_create(int device, int D, int F, int B, double eta, double lambda, sl_handle** out);
+int sl_destroy(sl_handle* h);
+/* Text of the last failure on this handle (h == NULL: last sl_create failure). */
+const char* sl_last_error(const sl_handle* h);
+
+/* Tuning / introspection knobs (DESIGN.md lists the keys). */
+int sl_set_option(sl_handle* h, const char* key, long long value);
+long long sl_get_info(sl_handle* h, const char* key);
+
+/* ---- shard ingest --------------------------------------------------------------
+ * Replaces the body of Worker::ReceiveFile (src/worker.cc:49-61), whose loop reads
+ * each Chunk and drops it.  Call sl_shard_begin once per stream, sl_shard_append
+ * once per Chunk (any length, any alignment; rows may straddle calls) and
+ * sl_shard_end when reader->Read returns false.  Bytes go through a pinned ring to
+ * a resident HBM buffer; a pinned source is DMA'd directly.  The byte stream is
+ * kept verbatim: n_rows = floor(len / (4*(F+1))); the first n_rows*F fp32 are X
+ * (row-major), the next n_rows fp32 are the labels.  size_hint = expected length
+ * in bytes (0 = unknown, the buffer then grows by doubling). */
+int sl_shard_begin(sl_handle* h, size_t size_hint);
+int sl_shard_append(sl_handle* h, const void* bytes, size_t n);
+int sl_shard_end(sl_handle* h, long long* n_rows /* nullable */);
+/* Device-side check of what arrived: byte_sum = sum b[i], weighted = sum (i+1)*b[i]
+ * (both mod 2^64) over the sealed shard's bytes.  Used for the file-0 parity gate
+ * (src/file_server.cc:152-156). */
+int sl_shard_checksum(sl_handle* h, unsigned long long* byte_sum, unsigned long long* weighted);
+/* Copy n bytes at offset of the sealed shard back to the host (tests). */
+int sl_shard_read(sl_handle* h, size_t offset, void* out, size_t n);
+long long sl_shard_bytes(sl_handle* h);
+/* Fill the shard on the device with rows [row0, row0+n_rows) of the synthetic
+ * matrix of SURVEY.md §8(d) (bit-identical to the oracle's generator) and seal it. */
+int sl_shard_synth(sl_handle* h, long long n_rows, unsigned long long row0,
+                   unsigned long long seed);
+
+/* ---- training ------------------------------------------------------------------
+ * sl_train_tick replaces one iteration of simulate_training (src/worker.cc:225-227:
+ * model[i] += 1) and exists for parity with the reference as it stands.
+ * sl_train_steps is what takes that slot in this build: n_steps minibatch steps of
+ * logistic regression over the resident shard, rows (t*B + j) mod n_rows, t
+ * continuing from the previous call (reset by sl_shard_end).  loss_out (nullable)
+ * receives n_steps mean losses.  Blocks until the steps are done. */
+int sl_train_tick(sl_handle* h);
+int sl_train_steps(sl_handle* h, int n_steps, double* loss_out);
+/* Device time (CUDA events on the handle's stream) of the kernels of the last
+ * sl_train_steps / sl_train_steps_sync call, in milliseconds. */
+float sl_last_train_ms(sl_handle* h);
+
+/* ---- update exchange -------------------------------------------------------------
+ * sl_merge: callee side, the loop of MasterImpl::ExchangeUpdates
+ * (src/master.cc:99-110) == WorkerImpl::ExchangeUpdates (src/worker.cc:85-96):
+ *   model += lambda*delta_in; reply = model - old; old = model     — one kernel.
+ * n_in and n_out must equal D (the reference zero-extends or reads out of bounds).
+ * sl_delta_snapshot: initiator's delta build (src/worker.cc:205-208).
+ * sl_apply_reply: initiator's apply (src/worker.cc:161-162) followed by
+ *   old = model (src/worker.cc:215).
+ * All three are bit-exact fp64 (rounded multiply, then rounded add). */
+int sl_merge(sl_handle* h, const double* delta_in, int n_in, double* reply_out, int n_out);
+int sl_delta_snapshot(sl_handle* h, double* out, int n);
+int sl_apply_reply(sl_handle* h, const double* back, int n);
+int sl_get_model(sl_handle* h, double* out, int n);
+int sl_get_old(sl_handle* h, double* out, int n);
+/* Overwrite the replica (tests, checkpoint restore).  old may be NULL = keep. */
+int sl_set_state(sl_handle* h, const double* model, const double* old, int n);
+
+/* ---- same-box data parallel (one handle per GPU, one process per GPU) ---------------
+ * Build-defined extension (the reference only has asynchronous pairwise gossip):
+ * every step each rank takes its local gradient and all ranks apply the mean.
+ * sl_comm_unique_id fills 128 bytes on one rank; broadcast them by any means and
+ * call sl_comm_init_rank on every rank.  NCCL is resolved with dlopen at that
+ * point.  sl_allreduce_avg: model <- mean over ranks of model (one ncclAllReduce).
+ * sl_train_steps_sync: n_steps of { local gradient; all-reduce; update }. */
+int sl_comm_unique_id(void* id128);
+int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128);
+int sl_allreduce_avg(sl_handle* h);
+int sl_train_steps_sync(sl_handle* h, int n_steps, double* loss_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SL_GPU_H */

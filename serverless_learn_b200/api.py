@@ -1,0 +1,195 @@
+"""`Replica`: one model replica (a worker, or the master) on one GPU — a 1:1 wrapper of
+the sl_* C ABI.  Method names follow the reference's handlers and loops:
+
+    receive_file(chunks)      Worker::ReceiveFile            src/worker.cc:49-61
+    exchange_updates(delta)   {Master,Worker}Impl::ExchangeUpdates  src/master.cc:95-114
+    delta() / apply_reply()   periodically_gossip + WorkerStub::ExchangeUpdates
+                                                             src/worker.cc:145-172,194-219
+    train_tick()              simulate_training              src/worker.cc:221-231
+    train_steps(n)            the minibatch step that takes simulate_training's slot
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+_dp = C.POINTER(C.c_double)
+
+
+class SlError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"sl error {code}: {msg}")
+        self.code = code
+
+
+def _d(a: np.ndarray):
+    return a.ctypes.data_as(_dp)
+
+
+class Replica:
+    def __init__(self, F: int, B: int, eta: float = 0.1, lam: float = 0.5, device: int = 0,
+                 D: int | None = None):
+        self._L = _lib.load()
+        self._h = C.c_void_p()
+        self.F, self.B, self.D = F, B, F if D is None else D
+        rc = self._L.sl_create(device, self.D, F, B, eta, lam, C.byref(self._h))
+        if rc != 0:
+            msg = self._L.sl_last_error(None)
+            self._h = C.c_void_p()
+            raise SlError(rc, msg.decode() if msg else "?")
+
+    # ---- plumbing -----------------------------------------------------------------
+    def _ck(self, rc: int):
+        if rc != 0:
+            msg = self._L.sl_last_error(self._h)
+            raise SlError(rc, msg.decode() if msg else "?")
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.sl_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def set_option(self, key: str, value: int):
+        self._ck(self._L.sl_set_option(self._h, key.encode(), int(value)))
+
+    def info(self, key: str) -> int:
+        return int(self._L.sl_get_info(self._h, key.encode()))
+
+    # ---- ingest -------------------------------------------------------------------
+    def shard_begin(self, size_hint: int = 0):
+        self._ck(self._L.sl_shard_begin(self._h, size_hint))
+
+    def shard_append(self, data) -> None:
+        if isinstance(data, (bytes, bytearray, memoryview)):
+            buf = np.frombuffer(data, dtype=np.uint8)
+        else:
+            buf = np.ascontiguousarray(data).view(np.uint8).reshape(-1)
+        self._ck(self._L.sl_shard_append(self._h, buf.ctypes.data, buf.size))
+
+    def shard_append_ptr(self, ptr: int, nbytes: int) -> None:
+        self._ck(self._L.sl_shard_append(self._h, C.c_void_p(ptr), nbytes))
+
+    def shard_end(self) -> int:
+        n = C.c_longlong()
+        self._ck(self._L.sl_shard_end(self._h, C.byref(n)))
+        return n.value
+
+    def receive_file(self, chunks) -> bool:
+        """Worker::ReceiveFile: consume a stream of Chunk payloads; returns the ack's ok."""
+        try:
+            self.shard_begin(0)
+            for ch in chunks:
+                self.shard_append(ch)
+            self.shard_end()
+            return True
+        except SlError:
+            return False
+
+    def load_shard(self, X: np.ndarray, y: np.ndarray) -> int:
+        """Stream a shard in the wire layout (X bytes then y bytes)."""
+        X = np.ascontiguousarray(X, dtype=np.float32)
+        y = np.ascontiguousarray(y, dtype=np.float32)
+        assert X.shape[0] == y.shape[0] and X.shape[1] == self.F
+        self.shard_begin(X.nbytes + y.nbytes)
+        self.shard_append(X)
+        self.shard_append(y)
+        return self.shard_end()
+
+    def shard_synth(self, n_rows: int, row0: int = 0, seed: int = 0x5EED):
+        self._ck(self._L.sl_shard_synth(self._h, n_rows, row0, seed))
+
+    def shard_checksum(self):
+        a, b = C.c_ulonglong(), C.c_ulonglong()
+        self._ck(self._L.sl_shard_checksum(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def shard_read(self, offset: int, n: int) -> np.ndarray:
+        out = np.empty(n, dtype=np.uint8)
+        self._ck(self._L.sl_shard_read(self._h, offset, out.ctypes.data, n))
+        return out
+
+    def shard_bytes(self) -> int:
+        return int(self._L.sl_shard_bytes(self._h))
+
+    # ---- training -----------------------------------------------------------------
+    def train_tick(self):
+        self._ck(self._L.sl_train_tick(self._h))
+
+    def train_steps(self, n_steps: int, want_loss: bool = True):
+        loss = np.empty(max(n_steps, 1), dtype=np.float64)
+        self._ck(self._L.sl_train_steps(self._h, n_steps, _d(loss) if want_loss else None))
+        return loss[:n_steps] if want_loss else None
+
+    def train_steps_sync(self, n_steps: int, want_loss: bool = True):
+        loss = np.empty(max(n_steps, 1), dtype=np.float64)
+        self._ck(self._L.sl_train_steps_sync(self._h, n_steps, _d(loss) if want_loss else None))
+        return loss[:n_steps] if want_loss else None
+
+    def last_train_ms(self) -> float:
+        return float(self._L.sl_last_train_ms(self._h))
+
+    # ---- exchange -----------------------------------------------------------------
+    def exchange_updates(self, delta_in: np.ndarray) -> np.ndarray:
+        """Callee side of ExchangeUpdates: returns the reply delta."""
+        delta_in = np.ascontiguousarray(delta_in, dtype=np.float64)
+        reply = np.empty(self.D, dtype=np.float64)
+        self._ck(self._L.sl_merge(self._h, _d(delta_in), delta_in.size, _d(reply), reply.size))
+        return reply
+
+    def delta(self) -> np.ndarray:
+        out = np.empty(self.D, dtype=np.float64)
+        self._ck(self._L.sl_delta_snapshot(self._h, _d(out), out.size))
+        return out
+
+    def apply_reply(self, back: np.ndarray) -> None:
+        back = np.ascontiguousarray(back, dtype=np.float64)
+        self._ck(self._L.sl_apply_reply(self._h, _d(back), back.size))
+
+    def model(self) -> np.ndarray:
+        out = np.empty(self.D, dtype=np.float64)
+        self._ck(self._L.sl_get_model(self._h, _d(out), out.size))
+        return out
+
+    def old(self) -> np.ndarray:
+        out = np.empty(self.D, dtype=np.float64)
+        self._ck(self._L.sl_get_old(self._h, _d(out), out.size))
+        return out
+
+    def set_state(self, model=None, old=None):
+        m = None if model is None else np.ascontiguousarray(model, dtype=np.float64)
+        o = None if old is None else np.ascontiguousarray(old, dtype=np.float64)
+        n = m.size if m is not None else o.size
+        self._ck(self._L.sl_set_state(self._h, _d(m) if m is not None else None,
+                                      _d(o) if o is not None else None, n))
+
+    # ---- same-box data parallel ----------------------------------------------------
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        L = _lib.load()
+        buf = C.create_string_buffer(128)
+        rc = L.sl_comm_unique_id(buf)
+        if rc != 0:
+            raise SlError(rc, (L.sl_last_error(None) or b"?").decode())
+        return buf.raw
+
+    def comm_init_rank(self, nranks: int, rank: int, uid: bytes):
+        buf = C.create_string_buffer(uid, 128)
+        self._ck(self._L.sl_comm_init_rank(self._h, nranks, rank, buf))
+
+    def allreduce_avg(self):
+        self._ck(self._L.sl_allreduce_avg(self._h))

@@ -1,0 +1,849 @@
+// sl_gpu.cu — the C ABI of include/sl_gpu.h: handle, staging, launches.
+// There is no CPU fallback anywhere in this file: every entry point runs on the GPU
+// or returns an error.
+#include "../../include/sl_gpu.h"
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+namespace {
+
+thread_local std::string g_create_error;
+
+constexpr int kStageSlots = 4;
+constexpr size_t kStageBytes = 8u << 20;
+constexpr int kMaxStepsPerLaunch = 1 << 15;
+constexpr size_t kDefaultShardCap = 256u << 20;
+
+// ---- NCCL, resolved at run time (sl_comm_init_rank) -------------------------------
+typedef struct ncclComm* ncclComm_t;
+struct NcclUniqueId { char internal[128]; };
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(NcclUniqueId*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, NcclUniqueId, int) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclFloat64 = 8;  // ncclDataType_t::ncclFloat64
+constexpr int kNcclSum = 0;      // ncclRedOp_t::ncclSum
+NcclApi g_nccl;
+std::mutex g_nccl_mu;
+
+const char* load_nccl() {
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (g_nccl.lib) return nullptr;
+    // a process that already imported torch has its bundled libnccl.so.2 mapped;
+    // dlopen by soname returns that copy instead of loading a second NCCL.
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    void* lib = nullptr;
+    for (const char* n : names) {
+        lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (lib) break;
+    }
+    if (!lib) return "libnccl.so.2 not found (dlopen)";
+    NcclApi api;
+    api.lib = lib;
+    api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))dlsym(lib, "ncclCommInitRank");
+    api.AllReduce = (decltype(api.AllReduce))dlsym(lib, "ncclAllReduce");
+    api.CommDestroy = (decltype(api.CommDestroy))dlsym(lib, "ncclCommDestroy");
+    api.GetErrorString = (decltype(api.GetErrorString))dlsym(lib, "ncclGetErrorString");
+    if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy)
+        return "NCCL symbols missing";
+    g_nccl = api;
+    return nullptr;
+}
+
+// ---- persistent-kernel variants -----------------------------------------------------
+struct Variant {
+    int ch, r, ncw;
+    const void* fn;
+};
+#define SL_VARIANT(CH, R, NCW) \
+    Variant { CH, R, NCW, (const void*)slk::lr_persist_kernel<CH, R, NCW> }
+const Variant kVariants[] = {
+    SL_VARIANT(1, 16, 16),  // 1: F <= 2048, 32 rows per sub-batch at F = 1024
+    SL_VARIANT(1, 8, 16),   // 2
+    SL_VARIANT(1, 32, 8),   // 3: F <= 1024, 8 consumer warps
+    SL_VARIANT(2, 8, 16),   // 4: F <= 4096
+    SL_VARIANT(4, 4, 16),   // 5: F <= 8192
+    SL_VARIANT(8, 2, 8),    // 6: F <= 8192, 8 warps
+    SL_VARIANT(16, 1, 8),   // 7: F <= 16384
+};
+constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
+
+}  // namespace
+
+struct sl_handle {
+    int device = 0;
+    int D = 0, F = 0, B = 0;
+    double eta = 0, lambda = 0;
+    int num_sms = 0, coop = 0;
+    size_t smem_optin = 0;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+
+    double *model = nullptr, *old = nullptr;  // device fp64 [D]
+    // exchange staging: pinned + mapped, the kernels read / write it directly
+    double *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
+    int *h_err = nullptr, *d_err = nullptr;
+    unsigned long long *h_sum = nullptr, *d_sum = nullptr;
+
+    // shard
+    unsigned char* shard = nullptr;
+    size_t shard_cap = 0, shard_len = 0;
+    long long n_rows = 0;
+    bool shard_open = false, shard_sealed = false;
+    unsigned char* stage[kStageSlots] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t stage_ev[kStageSlots] = {nullptr, nullptr, nullptr, nullptr};
+    int stage_idx = 0;
+
+    // training scratch
+    long long step = 0;
+    unsigned flag_base = 0;
+    uint4 *part_ll = nullptr, *w_ll = nullptr;
+    size_t part_ll_bytes = 0;
+    int ll_grid = 0;
+    double* d_loss = nullptr;
+    double* h_loss = nullptr;
+    size_t loss_cap = 0;
+    float *resid = nullptr, *rowloss = nullptr, *gpart = nullptr;
+    double* gsum = nullptr;
+    int nsplit = 0, rows_per_split = 0;
+
+    // options
+    long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
+    // info
+    long long launches = 0, path_used = 0, variant_used = 0, grid_used = 0, ns_used = 0,
+              smem_used = 0;
+
+    // NCCL
+    ncclComm_t comm = nullptr;
+    int nranks = 1, rank = 0;
+
+    std::mutex mu;
+    std::string err;
+};
+
+namespace {
+
+int fail(sl_handle* h, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (h) h->err = buf;
+    else g_create_error = buf;
+    return code;
+}
+
+#define CK(h, call)                                                                      \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess)                                                           \
+            return fail((h), SL_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                        __FILE__, __LINE__);                                             \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+int ensure_shard_cap(sl_handle* h, size_t need) {
+    if (need <= h->shard_cap) return SL_OK;
+    size_t cap = std::max(need, std::max(h->shard_cap * 2, kDefaultShardCap));
+    unsigned char* nb = nullptr;
+    cudaError_t e = cudaMalloc(&nb, cap);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(h, SL_ENOMEM, "cudaMalloc(%zu) for the shard failed: %s", cap,
+                    cudaGetErrorString(e));
+    }
+    if (h->shard && h->shard_len) {
+        CK(h, cudaMemcpyAsync(nb, h->shard, h->shard_len, cudaMemcpyDeviceToDevice, h->copy_stream));
+        CK(h, cudaStreamSynchronize(h->copy_stream));
+    }
+    if (h->shard) cudaFree(h->shard);
+    h->shard = nb;
+    h->shard_cap = cap;
+    return SL_OK;
+}
+
+// geometry of the simple path
+int ensure_simple_scratch(sl_handle* h) {
+    if (h->resid) return SL_OK;
+    const int col_blocks = (h->F + 127) / 128;
+    int want = std::max(1, (4 * h->num_sms + col_blocks - 1) / col_blocks);
+    want = std::min(want, h->B);
+    h->rows_per_split = (h->B + want - 1) / want;
+    h->nsplit = (h->B + h->rows_per_split - 1) / h->rows_per_split;
+    CK(h, cudaMalloc(&h->resid, sizeof(float) * h->B));
+    CK(h, cudaMalloc(&h->rowloss, sizeof(float) * h->B));
+    CK(h, cudaMalloc(&h->gpart, sizeof(float) * (size_t)h->nsplit * h->F));
+    CK(h, cudaMalloc(&h->gsum, sizeof(double) * (h->F + 1)));
+    return SL_OK;
+}
+
+int ensure_loss_cap(sl_handle* h, size_t n) {
+    if (n <= h->loss_cap) return SL_OK;
+    if (h->d_loss) cudaFree(h->d_loss);
+    if (h->h_loss) cudaFreeHost(h->h_loss);
+    h->d_loss = nullptr;
+    h->h_loss = nullptr;
+    h->loss_cap = 0;
+    size_t cap = std::max<size_t>(n, 1024);
+    CK(h, cudaMalloc(&h->d_loss, sizeof(double) * cap));
+    CK(h, cudaMallocHost(&h->h_loss, sizeof(double) * cap));
+    h->loss_cap = cap;
+    return SL_OK;
+}
+
+struct PersistPlan {
+    int variant = -1;  // index into kVariants
+    int grid = 0;
+    slk::LrArgs args;
+    size_t smem = 0;
+};
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Returns false (with reason) when the persistent kernel cannot run this shape.
+bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
+    const int F = h->F;
+    if (!h->coop) { *why = "device lacks cooperative launch"; return false; }
+    if (F % 4 != 0) { *why = "F is not a multiple of 4 (16-byte rows needed)"; return false; }
+    if (((uintptr_t)h->shard & 15) != 0) { *why = "shard not 16-byte aligned"; return false; }
+    const int granules = F / 4;
+    int vi = -1;
+    if (h->opt_variant > 0 && h->opt_variant <= kNumVariants) {
+        vi = (int)h->opt_variant - 1;
+        if (granules > kVariants[vi].ch * 32 * kVariants[vi].ncw) {
+            *why = "requested variant too narrow for F";
+            return false;
+        }
+    } else {
+        for (int i = 0; i < kNumVariants; ++i) {
+            if (granules <= kVariants[i].ch * 32 * kVariants[i].ncw) { vi = i; break; }
+        }
+        if (vi < 0) { *why = "F too wide for the persistent kernel"; return false; }
+    }
+    const Variant& v = kVariants[vi];
+    int grid = h->num_sms;
+    if (h->opt_grid > 0) grid = (int)std::min<long long>(h->opt_grid, h->num_sms);
+    slk::LrArgs& a = p->args;
+    memset(&a, 0, sizeof(a));
+    a.F = F;
+    a.B = h->B;
+    a.Q = F / 2 + 1;
+    a.qpc = (a.Q + grid - 1) / grid;
+    a.wpg = (granules + v.ch * 32 - 1) / (v.ch * 32);
+    a.row_bytes = 4 * F;
+    const int rg = v.ncw / a.wpg;
+    // fixed shared-memory regions after the ring
+    const size_t red_b = sizeof(float) * 2 * v.ncw * v.r;
+    const size_t lsm_b = sizeof(float) * v.ncw;
+    const size_t own_b = sizeof(double) * 2 * a.qpc;
+    const size_t gsm_b = sizeof(float) * (size_t)std::max(0, rg - 1) * F;
+    const size_t fixed = red_b + lsm_b + own_b + gsm_b + 256;
+    if (h->smem_optin < fixed + 16 + (size_t)a.row_bytes) {
+        *why = "row does not fit in shared memory";
+        return false;
+    }
+    size_t ns = (h->smem_optin - fixed) / ((size_t)a.row_bytes + 8);
+    ns = std::min<size_t>(ns, 1024);
+    if (ns < 1) { *why = "no ring slot fits"; return false; }
+    a.ns = (int)ns;
+    size_t off = (size_t)a.ns * a.row_bytes;
+    off = align_up(off, 16); a.off_full = (int)off;  off += 8 * ns;
+    off = align_up(off, 16); a.off_red = (int)off;   off += red_b;
+    a.off_lsm = (int)off;                            off += lsm_b;
+    off = align_up(off, 16); a.off_own = (int)off;   off += own_b;
+    off = align_up(off, 16); a.off_gsm = (int)off;   off += gsm_b;
+    p->smem = off;
+    p->variant = vi;
+    p->grid = grid;
+    return true;
+}
+
+int ensure_ll(sl_handle* h, int grid, int Q) {
+    const size_t need = sizeof(uint4) * (size_t)grid * Q;
+    if (h->part_ll && h->part_ll_bytes >= need && h->ll_grid == grid) return SL_OK;
+    if (h->part_ll) cudaFree(h->part_ll);
+    if (h->w_ll) cudaFree(h->w_ll);
+    h->part_ll = nullptr;
+    h->w_ll = nullptr;
+    CK(h, cudaMalloc(&h->part_ll, need));
+    CK(h, cudaMalloc(&h->w_ll, sizeof(uint4) * Q));
+    // flag 0 is never expected first (flags start at flag_base + 1 >= 1)
+    CK(h, cudaMemsetAsync(h->part_ll, 0, need, h->stream));
+    CK(h, cudaMemsetAsync(h->w_ll, 0, sizeof(uint4) * Q, h->stream));
+    h->part_ll_bytes = need;
+    h->ll_grid = grid;
+    h->flag_base = 0;
+    return SL_OK;
+}
+
+int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_loss) {
+    const Variant& v = kVariants[plan.variant];
+    int rc = ensure_ll(h, plan.grid, plan.args.Q);
+    if (rc) return rc;
+    CK(h, cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
+    int occ = 0;
+    CK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, v.ncw * 32, plan.smem));
+    if (occ < 1) return fail(h, SL_ECUDA, "persistent kernel does not fit on an SM");
+    const int max_per_launch =
+        h->opt_steps_per_launch > 0 ? (int)h->opt_steps_per_launch : kMaxStepsPerLaunch;
+    int done = 0;
+    *h->h_err = 0;
+    while (done < n_steps) {
+        const int n = std::min(max_per_launch, n_steps - done);
+        // 32-bit flag wrap: equality compare makes wrap harmless, but never emit flag 0
+        // as a "first" flag right after the zero-fill
+        slk::LrArgs a = plan.args;
+        a.X = reinterpret_cast<const float*>(h->shard);
+        a.y = a.X + (size_t)h->n_rows * h->F;
+        a.n_rows = h->n_rows;
+        a.step0 = h->step;
+        a.n_steps = n;
+        a.model = h->model;
+        a.part_ll = h->part_ll;
+        a.w_ll = h->w_ll;
+        a.loss_out = want_loss ? h->d_loss + done : nullptr;
+        a.flag0 = h->flag_base;
+        a.eta_over_b = h->eta / (double)h->B;
+        a.err = h->d_err;
+        void* params[] = {&a};
+        CK(h, cudaLaunchCooperativeKernel(v.fn, dim3(plan.grid), dim3(v.ncw * 32), params,
+                                          plan.smem, h->stream));
+        h->launches++;
+        h->step += n;
+        h->flag_base += (unsigned)n;
+        done += n;
+    }
+    h->path_used = 1;
+    h->variant_used = plan.variant + 1;
+    h->grid_used = plan.grid;
+    h->ns_used = plan.args.ns;
+    h->smem_used = (long long)plan.smem;
+    return SL_OK;
+}
+
+// one step of the simple path; sync != 0 adds the all-reduce between finish and apply
+int launch_simple_step(sl_handle* h, double* d_loss_slot, bool sync) {
+    const float* X = reinterpret_cast<const float*>(h->shard);
+    const float* y = X + (size_t)h->n_rows * h->F;
+    const long long mb = (long long)(((__int128)h->step * h->B) % h->n_rows);
+    const int wpb = 8;
+    slk::lr_fwd_kernel<<<(h->B + wpb - 1) / wpb, wpb * 32, 0, h->stream>>>(
+        X, y, h->n_rows, h->F, h->B, mb, h->model, h->resid, h->rowloss);
+    dim3 gg((h->F + 127) / 128, h->nsplit);
+    slk::lr_grad_kernel<<<gg, 128, 0, h->stream>>>(X, h->n_rows, h->F, h->B, mb, h->resid, h->gpart,
+                                                   h->rows_per_split);
+    const int fb = (h->F + 255) / 256;
+    const double eob = h->eta / (double)h->B;
+    slk::lr_finish_kernel<<<fb, 256, 0, h->stream>>>(h->gpart, h->nsplit, h->F, h->B, h->rowloss,
+                                                     h->model, eob, d_loss_slot, h->gsum,
+                                                     sync ? 1 : 0);
+    h->launches += 3;
+    if (sync) {
+        int nrc = g_nccl.AllReduce(h->gsum, h->gsum, (size_t)h->F + 1, kNcclFloat64, kNcclSum,
+                                   h->comm, h->stream);
+        if (nrc != 0)
+            return fail(h, SL_ENCCL, "ncclAllReduce failed: %s",
+                        g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "?");
+        slk::lr_apply_avg_kernel<<<fb, 256, 0, h->stream>>>(
+            h->model, h->gsum, h->F, eob / (double)h->nranks, d_loss_slot,
+            1.0 / ((double)h->B * (double)h->nranks));
+        h->launches += 1;
+    }
+    CK(h, cudaGetLastError());
+    h->step += 1;
+    return SL_OK;
+}
+
+int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
+    if (n_steps < 0) return fail(h, SL_EINVAL, "n_steps < 0");
+    if (!h->shard_sealed || h->n_rows <= 0)
+        return fail(h, SL_ESTATE, "no sealed shard with at least one row (sl_shard_end first)");
+    if (sync && !h->comm) return fail(h, SL_ESTATE, "sl_comm_init_rank has not been called");
+    if (n_steps == 0) return SL_OK;
+    DeviceGuard dg(h->device);
+    int rc = ensure_loss_cap(h, (size_t)n_steps);
+    if (rc) return rc;
+    PersistPlan plan;
+    std::string why;
+    bool persist = !sync && h->opt_path != 2 && plan_persist(h, &plan, &why);
+    if (!sync && h->opt_path == 1 && !persist)
+        return fail(h, SL_EINVAL, "persistent path requested but unavailable: %s", why.c_str());
+    CK(h, cudaEventRecord(h->ev0, h->stream));
+    if (persist) {
+        rc = run_persist(h, plan, n_steps, loss_out != nullptr);
+        if (rc) return rc;
+    } else {
+        rc = ensure_simple_scratch(h);
+        if (rc) return rc;
+        for (int s = 0; s < n_steps; ++s) {
+            rc = launch_simple_step(h, loss_out ? h->d_loss + s : nullptr, sync);
+            if (rc) return rc;
+        }
+        h->path_used = sync ? 3 : 2;
+        h->variant_used = 0;
+    }
+    CK(h, cudaEventRecord(h->ev1, h->stream));
+    if (loss_out)
+        CK(h, cudaMemcpyAsync(h->h_loss, h->d_loss, sizeof(double) * n_steps, cudaMemcpyDeviceToHost,
+                              h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    CK(h, cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
+    if (*h->h_err != 0) {
+        const int code = *h->h_err;
+        *h->h_err = 0;
+        return fail(h, SL_ETIMEOUT, "in-kernel wait timed out (watchdog code %d)", code);
+    }
+    if (loss_out) memcpy(loss_out, h->h_loss, sizeof(double) * n_steps);
+    return SL_OK;
+}
+
+}  // namespace
+
+// =====================================================================================
+// C ABI
+// =====================================================================================
+extern "C" {
+
+int sl_create(int device, int D, int F, int B, double eta, double lambda, sl_handle** out) {
+    if (!out) return fail(nullptr, SL_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (D <= 0 || F <= 0 || B <= 0) return fail(nullptr, SL_EINVAL, "D, F and B must be positive");
+    if (D != F)
+        return fail(nullptr, SL_EINVAL,
+                    "D (%d) must equal F (%d): the model is bias-free logistic regression", D, F);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(nullptr, SL_ECUDA, "no CUDA device: %s (this library has no CPU fallback)",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    }
+    if (device < 0 || device >= ndev)
+        return fail(nullptr, SL_EINVAL, "device %d out of range [0,%d)", device, ndev);
+    sl_handle* h = new (std::nothrow) sl_handle();
+    if (!h) return fail(nullptr, SL_ENOMEM, "out of host memory");
+    h->device = device;
+    h->D = D; h->F = F; h->B = B; h->eta = eta; h->lambda = lambda;
+    DeviceGuard dg(device);
+#define CKC(call)                                                                          \
+    do {                                                                                   \
+        cudaError_t e_ = (call);                                                           \
+        if (e_ != cudaSuccess) {                                                           \
+            fail(nullptr, SL_ECUDA, "%s failed: %s", #call, cudaGetErrorString(e_));       \
+            sl_destroy(h);                                                                 \
+            return SL_ECUDA;                                                               \
+        }                                                                                  \
+    } while (0)
+    int v = 0;
+    CKC(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device));
+    h->num_sms = v;
+    CKC(cudaDeviceGetAttribute(&v, cudaDevAttrCooperativeLaunch, device));
+    h->coop = v;
+    CKC(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    h->smem_optin = (size_t)v;
+    CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CKC(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    CKC(cudaEventCreate(&h->ev0));
+    CKC(cudaEventCreate(&h->ev1));
+    CKC(cudaMalloc(&h->model, sizeof(double) * D));
+    CKC(cudaMalloc(&h->old, sizeof(double) * D));
+    CKC(cudaMemsetAsync(h->model, 0, sizeof(double) * D, h->stream));
+    CKC(cudaMemsetAsync(h->old, 0, sizeof(double) * D, h->stream));
+    CKC(cudaHostAlloc(&h->h_in, sizeof(double) * D, cudaHostAllocMapped));
+    CKC(cudaHostAlloc(&h->h_out, sizeof(double) * D, cudaHostAllocMapped));
+    CKC(cudaHostGetDevicePointer(&h->d_in, h->h_in, 0));
+    CKC(cudaHostGetDevicePointer(&h->d_out, h->h_out, 0));
+    CKC(cudaHostAlloc(&h->h_err, sizeof(int), cudaHostAllocMapped));
+    CKC(cudaHostGetDevicePointer(&h->d_err, h->h_err, 0));
+    *h->h_err = 0;
+    CKC(cudaHostAlloc(&h->h_sum, 2 * sizeof(unsigned long long), cudaHostAllocMapped));
+    CKC(cudaHostGetDevicePointer(&h->d_sum, h->h_sum, 0));
+    for (int i = 0; i < kStageSlots; ++i) {
+        CKC(cudaMallocHost(&h->stage[i], kStageBytes));
+        CKC(cudaEventCreateWithFlags(&h->stage_ev[i], cudaEventDisableTiming));
+    }
+    CKC(cudaStreamSynchronize(h->stream));
+#undef CKC
+    *out = h;
+    return SL_OK;
+}
+
+int sl_destroy(sl_handle* h) {
+    if (!h) return SL_OK;
+    DeviceGuard dg(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
+    if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    cudaFree(h->model); cudaFree(h->old); cudaFree(h->shard);
+    cudaFree(h->part_ll); cudaFree(h->w_ll); cudaFree(h->d_loss);
+    cudaFree(h->resid); cudaFree(h->rowloss); cudaFree(h->gpart); cudaFree(h->gsum);
+    if (h->h_in) cudaFreeHost(h->h_in);
+    if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->h_err) cudaFreeHost(h->h_err);
+    if (h->h_sum) cudaFreeHost(h->h_sum);
+    if (h->h_loss) cudaFreeHost(h->h_loss);
+    for (int i = 0; i < kStageSlots; ++i) {
+        if (h->stage[i]) cudaFreeHost(h->stage[i]);
+        if (h->stage_ev[i]) cudaEventDestroy(h->stage_ev[i]);
+    }
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    delete h;
+    return SL_OK;
+}
+
+const char* sl_last_error(const sl_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int sl_set_option(sl_handle* h, const char* key, long long value) {
+    if (!h || !key) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    std::string k(key);
+    if (k == "grid") h->opt_grid = value;
+    else if (k == "variant") h->opt_variant = value;
+    else if (k == "path") h->opt_path = value;  // 0 auto, 1 persistent only, 2 simple
+    else if (k == "steps_per_launch") h->opt_steps_per_launch = value;
+    else if (k == "step") h->step = value;
+    else return fail(h, SL_EINVAL, "unknown option '%s'", key);
+    return SL_OK;
+}
+
+long long sl_get_info(sl_handle* h, const char* key) {
+    if (!h || !key) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    std::string k(key);
+    if (k == "launches") return h->launches;
+    if (k == "path") return h->path_used;
+    if (k == "variant") return h->variant_used;
+    if (k == "grid") return h->grid_used;
+    if (k == "ring_slots") return h->ns_used;
+    if (k == "smem") return h->smem_used;
+    if (k == "num_sms") return h->num_sms;
+    if (k == "step") return h->step;
+    if (k == "n_rows") return h->n_rows;
+    if (k == "nranks") return h->nranks;
+    if (k == "num_variants") return kNumVariants;
+    return SL_EINVAL;
+}
+
+// ---- shard ingest -------------------------------------------------------------------
+int sl_shard_begin(sl_handle* h, size_t size_hint) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);
+    CK(h, cudaStreamSynchronize(h->stream));  // no kernel may still read the old shard
+    h->shard_len = 0;
+    h->n_rows = 0;
+    h->shard_sealed = false;
+    h->shard_open = true;
+    if (size_hint) {
+        int rc = ensure_shard_cap(h, size_hint);
+        if (rc) return rc;
+    }
+    return SL_OK;
+}
+
+int sl_shard_append(sl_handle* h, const void* bytes, size_t n) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->shard_open) return fail(h, SL_ESTATE, "sl_shard_append without sl_shard_begin");
+    if (n == 0) return SL_OK;
+    if (!bytes) return fail(h, SL_EINVAL, "bytes is NULL");
+    DeviceGuard dg(h->device);
+    int rc = ensure_shard_cap(h, h->shard_len + n);
+    if (rc) return rc;
+    cudaPointerAttributes at;
+    bool pinned = false;
+    if (cudaPointerGetAttributes(&at, bytes) == cudaSuccess) pinned = at.type == cudaMemoryTypeHost;
+    else cudaGetLastError();
+    if (pinned) {
+        // the caller's buffer is page-locked: DMA straight from it
+        CK(h, cudaMemcpyAsync(h->shard + h->shard_len, bytes, n, cudaMemcpyHostToDevice,
+                              h->copy_stream));
+        CK(h, cudaStreamSynchronize(h->copy_stream));  // caller owns the buffer only for the call
+    } else {
+        const unsigned char* src = static_cast<const unsigned char*>(bytes);
+        size_t off = 0;
+        while (off < n) {
+            const size_t m = std::min(kStageBytes, n - off);
+            const int s = h->stage_idx;
+            CK(h, cudaEventSynchronize(h->stage_ev[s]));  // slot's previous DMA done
+            memcpy(h->stage[s], src + off, m);
+            CK(h, cudaMemcpyAsync(h->shard + h->shard_len + off, h->stage[s], m,
+                                  cudaMemcpyHostToDevice, h->copy_stream));
+            CK(h, cudaEventRecord(h->stage_ev[s], h->copy_stream));
+            h->stage_idx = (s + 1) % kStageSlots;
+            off += m;
+        }
+    }
+    h->shard_len += n;
+    return SL_OK;
+}
+
+int sl_shard_end(sl_handle* h, long long* n_rows) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->shard_open) return fail(h, SL_ESTATE, "sl_shard_end without sl_shard_begin");
+    DeviceGuard dg(h->device);
+    CK(h, cudaStreamSynchronize(h->copy_stream));
+    h->shard_open = false;
+    h->shard_sealed = true;
+    h->n_rows = (long long)(h->shard_len / (4 * ((size_t)h->F + 1)));
+    h->step = 0;
+    if (n_rows) *n_rows = h->n_rows;
+    return SL_OK;
+}
+
+int sl_shard_checksum(sl_handle* h, unsigned long long* byte_sum, unsigned long long* weighted) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->shard_sealed) return fail(h, SL_ESTATE, "no sealed shard");
+    DeviceGuard dg(h->device);
+    h->h_sum[0] = 0;
+    h->h_sum[1] = 0;
+    if (h->shard_len) {
+        const int grid = h->num_sms * 8;
+        slk::checksum_kernel<<<grid, 256, 0, h->stream>>>(h->shard, h->shard_len, h->d_sum);
+        h->launches++;
+        CK(h, cudaGetLastError());
+    }
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (byte_sum) *byte_sum = h->h_sum[0];
+    if (weighted) *weighted = h->h_sum[1];
+    return SL_OK;
+}
+
+int sl_shard_read(sl_handle* h, size_t offset, void* out, size_t n) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->shard_sealed) return fail(h, SL_ESTATE, "no sealed shard");
+    if (offset + n > h->shard_len) return fail(h, SL_EINVAL, "read past the end of the shard");
+    DeviceGuard dg(h->device);
+    CK(h, cudaMemcpyAsync(out, h->shard + offset, n, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return SL_OK;
+}
+
+long long sl_shard_bytes(sl_handle* h) { return h ? (long long)h->shard_len : SL_EINVAL; }
+
+int sl_shard_synth(sl_handle* h, long long n_rows, unsigned long long row0,
+                   unsigned long long seed) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (n_rows <= 0) return fail(h, SL_EINVAL, "n_rows must be positive");
+    DeviceGuard dg(h->device);
+    CK(h, cudaStreamSynchronize(h->stream));
+    const size_t bytes = (size_t)n_rows * 4 * ((size_t)h->F + 1);
+    h->shard_len = 0;
+    int rc = ensure_shard_cap(h, bytes);
+    if (rc) return rc;
+    float* X = reinterpret_cast<float*>(h->shard);
+    float* y = X + (size_t)n_rows * h->F;
+    const size_t quads = ((size_t)n_rows * h->F + 3) / 4;
+    const int grid = (int)std::min<size_t>((quads + 255) / 256, (size_t)h->num_sms * 16);
+    slk::synth_kernel<<<grid, 256, 0, h->stream>>>(X, y, n_rows, h->F, row0, seed);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaStreamSynchronize(h->stream));
+    h->shard_len = bytes;
+    h->n_rows = n_rows;
+    h->shard_open = false;
+    h->shard_sealed = true;
+    h->step = 0;
+    return SL_OK;
+}
+
+// ---- training -----------------------------------------------------------------------
+int sl_train_tick(sl_handle* h) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);
+    slk::tick_kernel<<<(h->D + 255) / 256, 256, 0, h->stream>>>(h->model, h->D);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaStreamSynchronize(h->stream));
+    return SL_OK;
+}
+
+int sl_train_steps(sl_handle* h, int n_steps, double* loss_out) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return train_impl(h, n_steps, loss_out, false);
+}
+
+int sl_train_steps_sync(sl_handle* h, int n_steps, double* loss_out) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return train_impl(h, n_steps, loss_out, true);
+}
+
+float sl_last_train_ms(sl_handle* h) { return h ? h->last_ms : -1.f; }
+
+// ---- update exchange ------------------------------------------------------------------
+int sl_merge(sl_handle* h, const double* delta_in, int n_in, double* reply_out, int n_out) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (n_in != h->D || n_out != h->D)
+        return fail(h, SL_EINVAL, "sl_merge: lengths (%d in, %d out) must equal D = %d", n_in, n_out,
+                    h->D);
+    if (!delta_in || !reply_out) return fail(h, SL_EINVAL, "NULL buffer");
+    DeviceGuard dg(h->device);
+    memcpy(h->h_in, delta_in, sizeof(double) * h->D);
+    const int thr = 128, blocks = ((h->D + 1) / 2 + thr - 1) / thr;
+    slk::merge_kernel<<<blocks, thr, 0, h->stream>>>(h->model, h->old, h->d_in, h->d_out, h->D,
+                                                     h->lambda);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaStreamSynchronize(h->stream));
+    memcpy(reply_out, h->h_out, sizeof(double) * h->D);
+    return SL_OK;
+}
+
+int sl_delta_snapshot(sl_handle* h, double* out, int n) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (n != h->D) return fail(h, SL_EINVAL, "sl_delta_snapshot: n (%d) must equal D = %d", n, h->D);
+    if (!out) return fail(h, SL_EINVAL, "NULL buffer");
+    DeviceGuard dg(h->device);
+    const int thr = 128, blocks = ((h->D + 1) / 2 + thr - 1) / thr;
+    slk::delta_kernel<<<blocks, thr, 0, h->stream>>>(h->model, h->old, h->d_out, h->D);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaStreamSynchronize(h->stream));
+    memcpy(out, h->h_out, sizeof(double) * h->D);
+    return SL_OK;
+}
+
+int sl_apply_reply(sl_handle* h, const double* back, int n) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (n != h->D) return fail(h, SL_EINVAL, "sl_apply_reply: n (%d) must equal D = %d", n, h->D);
+    if (!back) return fail(h, SL_EINVAL, "NULL buffer");
+    DeviceGuard dg(h->device);
+    memcpy(h->h_in, back, sizeof(double) * h->D);
+    const int thr = 128, blocks = ((h->D + 1) / 2 + thr - 1) / thr;
+    slk::apply_kernel<<<blocks, thr, 0, h->stream>>>(h->model, h->old, h->d_in, h->D, h->lambda);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaStreamSynchronize(h->stream));
+    return SL_OK;
+}
+
+static int read_vec(sl_handle* h, const double* dev, double* out, int n) {
+    if (n != h->D) return fail(h, SL_EINVAL, "n (%d) must equal D = %d", n, h->D);
+    if (!out) return fail(h, SL_EINVAL, "NULL buffer");
+    DeviceGuard dg(h->device);
+    CK(h, cudaMemcpyAsync(h->h_out, dev, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    memcpy(out, h->h_out, sizeof(double) * n);
+    return SL_OK;
+}
+
+int sl_get_model(sl_handle* h, double* out, int n) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return read_vec(h, h->model, out, n);
+}
+
+int sl_get_old(sl_handle* h, double* out, int n) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return read_vec(h, h->old, out, n);
+}
+
+int sl_set_state(sl_handle* h, const double* model, const double* old, int n) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (n != h->D) return fail(h, SL_EINVAL, "n (%d) must equal D = %d", n, h->D);
+    DeviceGuard dg(h->device);
+    if (model) {
+        memcpy(h->h_in, model, sizeof(double) * n);
+        CK(h, cudaMemcpyAsync(h->model, h->h_in, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+    }
+    if (old) {
+        memcpy(h->h_in, old, sizeof(double) * n);
+        CK(h, cudaMemcpyAsync(h->old, h->h_in, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+    }
+    return SL_OK;
+}
+
+// ---- same-box data parallel -------------------------------------------------------------
+int sl_comm_unique_id(void* id128) {
+    if (!id128) return SL_EINVAL;
+    const char* why = load_nccl();
+    if (why) return fail(nullptr, SL_ENCCL, "%s", why);
+    NcclUniqueId id;
+    int rc = g_nccl.GetUniqueId(&id);
+    if (rc != 0) return fail(nullptr, SL_ENCCL, "ncclGetUniqueId failed (%d)", rc);
+    memcpy(id128, &id, sizeof(id));
+    return SL_OK;
+}
+
+int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128) {
+    if (!h || !id128) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (nranks < 1 || rank < 0 || rank >= nranks) return fail(h, SL_EINVAL, "bad rank/nranks");
+    const char* why = load_nccl();
+    if (why) return fail(h, SL_ENCCL, "%s", why);
+    DeviceGuard dg(h->device);
+    NcclUniqueId id;
+    memcpy(&id, id128, sizeof(id));
+    int rc = g_nccl.CommInitRank(&h->comm, nranks, id, rank);
+    if (rc != 0)
+        return fail(h, SL_ENCCL, "ncclCommInitRank failed: %s",
+                    g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
+    h->nranks = nranks;
+    h->rank = rank;
+    return SL_OK;
+}
+
+int sl_allreduce_avg(sl_handle* h) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->comm) return fail(h, SL_ESTATE, "sl_comm_init_rank has not been called");
+    DeviceGuard dg(h->device);
+    int rc = g_nccl.AllReduce(h->model, h->model, (size_t)h->D, kNcclFloat64, kNcclSum, h->comm,
+                              h->stream);
+    if (rc != 0) return fail(h, SL_ENCCL, "ncclAllReduce failed (%d)", rc);
+    slk::scale_kernel<<<(h->D + 255) / 256, 256, 0, h->stream>>>(h->model, h->D,
+                                                                1.0 / (double)h->nranks);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaStreamSynchronize(h->stream));
+    return SL_OK;
+}
+
+}  // extern "C"
