@@ -62,6 +62,12 @@ const char* sl_last_error(const sl_handle* h);
 int sl_set_option(sl_handle* h, const char* key, long long value);
 long long sl_get_info(sl_handle* h, const char* key);
 
+/* Diagnostics: after sl_set_option(h, "debug_timeline", s) the next persistent launch
+ * records, for steps s..s+3 of that launch and every CTA, 8 (clock64, globaltimer) pairs
+ * at fixed points of the step; this reads them back ([4][grid][16] u64).  No
+ * counterpart in the reference. */
+int sl_debug_read(sl_handle* h, unsigned long long* out, size_t n_words);
+
 /* ---- shard ingest --------------------------------------------------------------
  * Replaces the body of Worker::ReceiveFile (src/worker.cc:49-61), whose loop reads
  * each Chunk and drops it.  Call sl_shard_begin once per stream, sl_shard_append

@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsl_gpu.so")
+LIB_PATH = os.environ.get("SL_GPU_LIB") or os.path.join(HERE, "libsl_gpu.so")
 
 SL_OK, SL_EINVAL, SL_ECUDA, SL_ESTATE, SL_ENOMEM, SL_ETIMEOUT, SL_ENCCL = 0, -1, -2, -3, -4, -5, -6
 
@@ -19,6 +19,7 @@ _SIGS = {
     "sl_last_error": (C.c_char_p, [_h]),
     "sl_set_option": (C.c_int, [_h, C.c_char_p, C.c_longlong]),
     "sl_get_info": (C.c_longlong, [_h, C.c_char_p]),
+    "sl_debug_read": (C.c_int, [_h, C.POINTER(C.c_ulonglong), C.c_size_t]),
     "sl_shard_begin": (C.c_int, [_h, C.c_size_t]),
     "sl_shard_append": (C.c_int, [_h, C.c_void_p, C.c_size_t]),
     "sl_shard_end": (C.c_int, [_h, C.POINTER(C.c_longlong)]),

@@ -65,17 +65,32 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
         "l"(src), "r"(bytes), "r"(bar), "l"(pol)
         : "memory");
 }
+// Packet loads / stores of the exchange.  SL_LL_MODE (experiments): 0 = volatile
+// (STRONG.SYS), 1 = relaxed.gpu both ways, 2 = relaxed.gpu loads + weak .cg stores.
+#ifndef SL_LL_MODE
+#define SL_LL_MODE 0
+#endif
 __device__ __forceinline__ uint4 ld_vol_v4(const uint4* p) {
     uint4 r;
+#if SL_LL_MODE == 0
     asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+#else
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+#endif
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                  : "l"(p)
                  : "memory");
     return r;
 }
 __device__ __forceinline__ void st_vol_v4(uint4* p, uint4 v) {
-    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
-                 "r"(v.z), "r"(v.w)
+#if SL_LL_MODE == 0
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};"
+#elif SL_LL_MODE == 1
+    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};"
+#else
+    asm volatile("st.global.cg.v4.u32 [%0], {%1,%2,%3,%4};"
+#endif
+                 ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                  : "memory");
 }
 __device__ __forceinline__ int ld_vol_s32(const int* p) {
@@ -104,8 +119,12 @@ constexpr int kErrTimeoutMbar = 1;
 constexpr int kErrTimeoutPart = 2;
 constexpr int kErrTimeoutW = 3;
 
+#ifndef SL_POLL_SLEEP
+#define SL_POLL_SLEEP 0
+#endif
 __device__ __forceinline__ bool spin_abort(uint32_t& spins, int* err, int code) {
     ++spins;
+    if (SL_POLL_SLEEP > 0) __nanosleep(SL_POLL_SLEEP);
     if ((spins & 1023u) == 0) {
         if (ld_vol_s32(err) != 0) return true;
         if (spins >= kSpinLimit) {
@@ -189,6 +208,31 @@ __device__ __forceinline__ float sigmoid_f(float z) { return 1.0f / (1.0f + expf
 // ------------------------------------------------------------------------------------
 // K1 — persistent minibatch-step kernel
 // ------------------------------------------------------------------------------------
+// Warp roles inside one CTA (one CTA per SM, persistent over all steps of the launch):
+//   warps [0, NCW)   compute: RG row groups x WPG warps; a thread owns CH float4 column
+//                    chunks of every row its group processes and the fp64 master copy of
+//                    the weights of those columns (every CTA updates all weights itself,
+//                    from the same exact integer gradient sum, so all replicas stay equal)
+//   warp  NCW        producer: one lane issues the TMA bulk copies of X, NS ring slots
+//                    ahead of the maths; never depends on the weights
+//   warp  NCW+1      exchange: one lane adds the CTA's gradient (fixed point, s64) into
+//                    a global accumulator with ONE TMA bulk reduction, bumps a counter,
+//                    waits until every CTA has done so and TMA-loads the total
+// Cross-CTA reduction = integer adds performed by L2 => exact, order-independent,
+// deterministic.  Accumulators are triple-buffered over steps and replicated KREP times
+// (CTA c uses replica c % KREP) so that a line is hit by G/KREP, not G, reductions.
+//
+// CH  float4 column chunks per thread per row        (F <= 4*CH*32*NCW)
+// R   rows per sub-batch of one row group (power of two), held in registers at once
+// RS  rows per ring slot (divides R): one bulk copy and one mbarrier per slot
+// XB  exchange through shared memory + TMA (F small enough for smem staging); otherwise
+//     per-element red.global.add.u64 and direct loads (wide rows, where a step is long)
+// WS  (wide rows) fp32 weights live in shared memory and the fp64 master in a per-CTA
+//     global scratch instead of registers
+constexpr int kFixShift = 36;                       // gradient fixed point: 2^-36 units
+constexpr double kFixScale = 68719476736.0;         // 2^36
+constexpr double kFixInv = 1.0 / 68719476736.0;
+
 struct LrArgs {
     const float* X;        // [n_rows, F] row-major, resident shard
     const float* y;        // [n_rows]
@@ -198,74 +242,194 @@ struct LrArgs {
     long long step0;       // global step index of the first step of this launch
     int n_steps;
     double* model;         // fp64 master weights [F] (model_state, src/master.cc:58)
-    uint4* part_ll;        // [grid][Q] gradient-partial packets  {v0, flag, v1, flag}
-    uint4* w_ll;           // [Q]       new-weight packets        {w0, flag, w1, flag}
+    unsigned long long* acc;   // [3][krep][Fp] s64 gradient accumulators (zero at launch)
+    unsigned* counter;     // arrivals; zero at launch
+    double* wmaster;       // WS only: [grid][F] per-CTA fp64 master copies
     double* loss_out;      // device [n_steps] or nullptr
-    unsigned flag0;        // step s of this launch uses flag0 + s + 1
     double eta_over_b;
     int* err;              // 0 = ok; set by the watchdog
     // geometry, computed on the host
-    int Q;                 // packets per vector: F/2 weights pairs + 1 loss packet
-    int qpc;               // packets owned (reduced) per CTA
+    int Fp;                // padded vector length: F + 2 (element F carries the loss)
+    int krep;              // accumulator replicas
     int wpg;               // warps per row group = ceil(F/4/CH/32)
-    int ns;                // ring slots (one row each)
+    int ns;                // ring slots (RS rows each)
     int row_bytes;         // 4*F
-    int off_full, off_red, off_lsm, off_own, off_gsm;  // smem offsets
+    int off_bar, off_red, off_lsm, off_gsm, off_gout, off_gin, off_wsm;  // smem offsets
+    // diagnostics (sl_set_option "debug_timeline"): [4 steps][grid][16] time stamps
+    unsigned long long* dbg;
+    int dbg_step;
 };
 
-// CH  float4 column chunks per thread per row        (F <= 4*CH*32*NCW)
-// R   rows per row group per sub-batch (power of two)
-// NCW warps per CTA.  There is no dedicated producer warp: the leader thread of a row
-// group re-arms a ring slot with the row NS positions ahead as soon as its group has
-// pulled the slot's row into registers ("refill on release"), so the TMA stream runs
-// NS rows ahead of the maths and never depends on the weights.
-template <int CH, int R, int NCW>
-__global__ void __launch_bounds__(NCW * 32, 1) lr_persist_kernel(const LrArgs a) {
+__device__ __forceinline__ void dbg_stamp(const LrArgs& a, int s, int point) {
+    if (a.dbg != nullptr && s >= a.dbg_step && s < a.dbg_step + 4) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        unsigned long long* d = a.dbg + ((size_t)(s - a.dbg_step) * gridDim.x + blockIdx.x) * 16;
+        d[2 * point] = (unsigned long long)clock64();
+        d[2 * point + 1] = t;
+    }
+}
+
+__device__ __forceinline__ void bulk_reduce_add_u64(void* gdst, uint32_t ssrc, uint32_t bytes) {
+    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.u64 [%0], [%1], %2;" ::"l"(gdst),
+                 "r"(ssrc), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_plain(uint32_t dst, const void* src, uint32_t bytes,
+                                               uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+        "l"(src), "r"(bytes), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_add_u32(unsigned* p, unsigned v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ long long to_fix(float v) { return __double2ll_rn((double)v * kFixScale); }
+
+template <int CH, int R, int RS, int NCW, bool XB, bool WS>
+__global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrArgs a) {
+    static_assert(R % RS == 0, "a sub-batch is a whole number of ring slots");
+    constexpr int SPB = R / RS;  // ring slots per sub-batch
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int c = blockIdx.x, G = gridDim.x;
 
     unsigned char* ring = smem;
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.off_full);
-    float* red = reinterpret_cast<float*>(smem + a.off_red);    // [2][NCW][R]
-    float* lsm = reinterpret_cast<float*>(smem + a.off_lsm);    // [NCW]
-    double* own_w = reinterpret_cast<double*>(smem + a.off_own);  // [2*qpc]
-    float* gsm = reinterpret_cast<float*>(smem + a.off_gsm);    // [RG-1][F]
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.off_bar);    // [ns]
+    uint64_t* empty = full + a.ns;                                     // [ns]
+    uint64_t* gfull = empty + a.ns;                                    // [1] gradient staged
+    uint64_t* wfull = gfull + 1;                                       // [1] total received
+    float* red = reinterpret_cast<float*>(smem + a.off_red);          // [2][NCW][R]
+    float* lsm = reinterpret_cast<float*>(smem + a.off_lsm);          // [NCW]
+    float* gsm = reinterpret_cast<float*>(smem + a.off_gsm);          // [RG-1][F]
+    long long* gout = reinterpret_cast<long long*>(smem + a.off_gout);  // XB: [Fp]
+    long long* gin = reinterpret_cast<long long*>(smem + a.off_gin);    // XB: [krep][Fp]
+    float* wsm = reinterpret_cast<float*>(smem + a.off_wsm);          // WS: [F]
 
     const int WPG = a.wpg, RG = NCW / WPG, CT = WPG * 32;
-    const int F = a.F, ns = a.ns, row_bytes = a.row_bytes;
+    const int F = a.F, Fp = a.Fp, ns = a.ns, row_bytes = a.row_bytes, KREP = a.krep;
+    const uint32_t slot_bytes = (uint32_t)RS * (uint32_t)row_bytes;
     const long long lo = ((long long)c * a.B) / G;
     const long long hi = ((long long)(c + 1) * a.B) / G;
-    const int nrows_c = (int)(hi - lo);  // this CTA's rows of every minibatch
-    const int rows_per_sb = R * RG;
-    const int nsb = (nrows_c + rows_per_sb - 1) / rows_per_sb;
-
-    const long long total_rows = (long long)a.n_steps * nrows_c;  // rows this CTA streams
-    const uint64_t pol = policy_evict_first();
-    // issue the TMA copy of this CTA's seq-th row into its ring slot
-    auto issue_row = [&](long long seq) {
-        const long long sp = seq / nrows_c;
-        const int ip = (int)(seq - sp * nrows_c);
-        const long long mbp = (long long)(((__int128)(a.step0 + sp) * a.B) % a.n_rows);
-        const long long grow = (mbp + lo + ip) % a.n_rows;
-        const uint32_t slot = (uint32_t)(seq % ns);
-        const uint32_t fb = smem_u32(&full[slot]);
-        mbar_arrive_expect_tx(fb, (uint32_t)row_bytes);
-        bulk_g2s(smem_u32(ring + (size_t)slot * row_bytes), a.X + (size_t)grow * F,
-                 (uint32_t)row_bytes, fb, pol);
+    const int nrows_c = (int)(hi - lo);             // this CTA's rows of every minibatch
+    const int nsl_c = (nrows_c + RS - 1) / RS;      // ... in ring slots
+    const int nst_c = (nrows_c + R - 1) / R;        // ... in sub-batch stages of R rows
+    const int nsb = (nst_c + RG - 1) / RG;          // sub-batches: one stage per row group
+    const long long mb0 = (long long)(((__int128)a.step0 * a.B) % a.n_rows);
+    const size_t acc_stride = (size_t)KREP * Fp;    // one step buffer
+    auto wrap = [&](long long v) {  // v mod n_rows; v < 2*n_rows in the common case
+        if (v >= a.n_rows) {
+            v -= a.n_rows;
+            if (v >= a.n_rows) v %= a.n_rows;
+        }
+        return v;
     };
+
     if (tid == 0) {
-        for (int s = 0; s < ns; ++s) mbar_init(smem_u32(&full[s]), 1);
+        for (int s = 0; s < ns; ++s) {
+            mbar_init(smem_u32(&full[s]), 1);
+            mbar_init(smem_u32(&empty[s]), WPG);
+        }
+        mbar_init(smem_u32(gfull), XB ? WPG : WPG * 32);
+        mbar_init(smem_u32(wfull), 1);
         fence_mbar_init();
-        const long long pre = total_rows < ns ? total_rows : ns;
-        for (long long q = 0; q < pre; ++q) issue_row(q);
     }
     __syncthreads();
 
+    // =========================================================================== producer
+    if (warp == NCW) {
+        if (lane == 0 && nsl_c > 0) {
+            const uint64_t pol = policy_evict_first();
+            uint32_t slot = 0, phase = 0;
+            long long mb = mb0;
+            for (int s = 0; s < a.n_steps; ++s) {
+                for (int q = 0; q < nsl_c; ++q) {
+                    mbar_wait(smem_u32(&empty[slot]), phase ^ 1u, a.err);
+                    const int rc = min(RS, nrows_c - q * RS);
+                    const uint32_t fb = smem_u32(&full[slot]);
+                    mbar_arrive_expect_tx(fb, (uint32_t)rc * (uint32_t)row_bytes);
+                    long long g0 = wrap(mb + lo + (long long)q * RS);
+                    uint32_t dst = smem_u32(ring + (size_t)slot * slot_bytes);
+                    int left = rc;
+                    while (left > 0) {  // one copy unless the rows wrap around the shard end
+                        const long long room = a.n_rows - g0;
+                        const int n = room < (long long)left ? (int)room : left;
+                        bulk_g2s(dst, a.X + (size_t)g0 * F, (uint32_t)n * (uint32_t)row_bytes, fb,
+                                 pol);
+                        dst += (uint32_t)n * (uint32_t)row_bytes;
+                        left -= n;
+                        g0 = 0;
+                    }
+                    if (++slot == (uint32_t)ns) { slot = 0; phase ^= 1u; }
+                }
+                mb = wrap(mb + a.B);
+            }
+        }
+        return;
+    }
+
+    // =========================================================================== exchange
+    if (warp == NCW + 1) {
+        for (int s = 0; s < a.n_steps; ++s) {
+            unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
+            // the CTA's gradient is staged (XB) or has been added by the compute threads
+            mbar_wait(smem_u32(gfull), (uint32_t)s & 1u, a.err);
+            if (lane == 0) {
+                if (XB) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    bulk_reduce_add_u64(buf + (size_t)(c % KREP) * Fp, smem_u32(gout),
+                                        (uint32_t)Fp * 8u);
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+                    asm volatile("fence.proxy.async;" ::: "memory");
+                }
+                red_release_add_u32(a.counter, 1u);
+                dbg_stamp(a, s, 3);
+                const unsigned want = (unsigned)G * (unsigned)(s + 1);
+                uint32_t spins = 0;
+                while ((int)(ld_relaxed_u32(a.counter) - want) < 0) {
+                    if (spin_abort(spins, a.err, kErrTimeoutPart)) break;
+                }
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                if (XB) {
+                    asm volatile("fence.proxy.async;" ::: "memory");
+                    const uint32_t wb = smem_u32(wfull);
+                    mbar_arrive_expect_tx(wb, (uint32_t)acc_stride * 8u);
+                    bulk_g2s_plain(smem_u32(gin), buf, (uint32_t)acc_stride * 8u, wb);
+                } else {
+                    mbar_arrive(smem_u32(wfull));
+                }
+                dbg_stamp(a, s, 4);
+            }
+            __syncwarp();
+            // Everybody has contributed to step s, hence finished reading the buffer of
+            // step s-1: clear this CTA's slice of it for step s+2.  The stores precede this
+            // warp's next release on the counter.
+            unsigned long long* z = a.acc + (size_t)((s + 2) % 3) * acc_stride;
+            for (size_t i = (size_t)c * 32 + lane; i < acc_stride; i += (size_t)G * 32) z[i] = 0ull;
+            __syncwarp();
+        }
+        return;
+    }
+
+    // =========================================================================== compute
     const int rg = warp / WPG, wig = warp - rg * WPG;
     const int ct = wig * 32 + lane;
     const bool active = rg < RG;  // warps beyond RG*WPG idle through the maths (still sync)
-    const bool leader = active && wig == 0 && lane == 0;  // re-arms this row group's slots
     const int ridx = row_of_lane<R>(lane);
     const bool canon = lane == lane_of_row<R>(ridx);
     constexpr int NCT = NCW * 32;
@@ -277,76 +441,173 @@ __global__ void __launch_bounds__(NCW * 32, 1) lr_persist_kernel(const LrArgs a)
         gq[ch] = ct + ch * CT;
         gv[ch] = active && (gq[ch] * 4 < F);
     }
-
-    // weights: fp32 working copy of the fp64 master
-    float4 w[CH];
+    // weights: fp64 master + fp32 working copy, per thread for its own columns
+    constexpr int NW = WS ? 1 : CH;
+    float4 w[NW];
+    double wm[NW][4];
+    const uint32_t wsm_a = smem_u32(wsm);
+    double* my_master = WS ? a.wmaster + (size_t)c * F : nullptr;
 #pragma unroll
     for (int ch = 0; ch < CH; ++ch) {
-        w[ch] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gv[ch]) {
-            const double* m = a.model + gq[ch] * 4;
-            w[ch] = make_float4((float)m[0], (float)m[1], (float)m[2], (float)m[3]);
+        if (!gv[ch]) {
+            if (!WS) { w[ch] = make_float4(0.f, 0.f, 0.f, 0.f); wm[ch][0] = wm[ch][1] = wm[ch][2] = wm[ch][3] = 0.0; }
+            continue;
+        }
+        const double* m = a.model + gq[ch] * 4;
+        const float4 wf = make_float4((float)m[0], (float)m[1], (float)m[2], (float)m[3]);
+        if (WS) {
+            if (rg == 0) {  // one group seeds the CTA's master copy; every group its own smem words
+                double* mm = my_master + gq[ch] * 4;
+                mm[0] = m[0]; mm[1] = m[1]; mm[2] = m[2]; mm[3] = m[3];
+            }
+            *reinterpret_cast<float4*>(wsm + gq[ch] * 4) = wf;
+        } else {
+            w[ch] = wf;
+            wm[ch][0] = m[0]; wm[ch][1] = m[1]; wm[ch][2] = m[2]; wm[ch][3] = m[3];
         }
     }
-    // packets this CTA reduces, and the fp64 master copy of the weights in them
-    const int q0 = min(a.Q, c * a.qpc), q1 = min(a.Q, (c + 1) * a.qpc);
-    for (int i = tid; i < 2 * (q1 - q0); i += NCT) {
-        const int col = 2 * q0 + i;
-        own_w[i] = col < F ? a.model[col] : 0.0;
-    }
-    named_bar_sync(1, NCT);
+    if (WS) named_bar_sync(1, NCT);
 
-    uint32_t base_slot = 0, base_phase = 0;
+    // apply the exact gradient total of step s to this thread's weights
+    auto apply_total = [&](int s) {
+        const unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
+#pragma unroll
+        for (int ch = 0; ch < CH; ++ch) {
+            if (!gv[ch]) continue;
+            long long t[4] = {0, 0, 0, 0};
+            if (XB) {
+                for (int k = 0; k < KREP; ++k) {
+                    const longlong2* p = reinterpret_cast<const longlong2*>(gin + (size_t)k * Fp + gq[ch] * 4);
+                    const longlong2 u = p[0], v = p[1];
+                    t[0] += u.x; t[1] += u.y; t[2] += v.x; t[3] += v.y;
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) t[e] = (long long)ld_relaxed_u64(buf + gq[ch] * 4 + e);
+            }
+            if (WS) {
+                if (rg == 0 || RG == 1) {
+                    double* mm = my_master + gq[ch] * 4;
+                    float4 wf;
+                    double v0 = mm[0] - a.eta_over_b * ((double)t[0] * kFixInv);
+                    double v1 = mm[1] - a.eta_over_b * ((double)t[1] * kFixInv);
+                    double v2 = mm[2] - a.eta_over_b * ((double)t[2] * kFixInv);
+                    double v3 = mm[3] - a.eta_over_b * ((double)t[3] * kFixInv);
+                    mm[0] = v0; mm[1] = v1; mm[2] = v2; mm[3] = v3;
+                    wf = make_float4((float)v0, (float)v1, (float)v2, (float)v3);
+                    *reinterpret_cast<float4*>(wsm + gq[ch] * 4) = wf;
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) wm[ch][e] -= a.eta_over_b * ((double)t[e] * kFixInv);
+                w[ch] = make_float4((float)wm[ch][0], (float)wm[ch][1], (float)wm[ch][2], (float)wm[ch][3]);
+            }
+        }
+        if (c == 0 && tid == 0 && a.loss_out) {
+            long long l = 0;
+            if (XB) for (int k = 0; k < KREP; ++k) l += gin[(size_t)k * Fp + F];
+            else l = (long long)ld_relaxed_u64(buf + F);
+            a.loss_out[s] = ((double)l * kFixInv) / (double)a.B;
+        }
+        if (WS && RG > 1) named_bar_sync(1, NCT);  // other groups read rg 0's smem weights
+    };
+
+    uint32_t base_slot = 0, base_phase = 0;  // ring position of this step's slot 0
     int red_buf = 0;
-    long long mb = (long long)(((__int128)a.step0 * a.B) % a.n_rows);
+    long long mb = mb0;
+    // label of the row this lane finishes, fetched one stage ahead of its use
+    auto load_y = [&](long long mbs, int j) -> float {
+        const int i = j * R + ridx;
+        return (active && j < nst_c && i < nrows_c) ? __ldg(a.y + (size_t)wrap(mbs + lo + i)) : 0.f;
+    };
+    float y_next = load_y(mb, rg);
 
     for (int s = 0; s < a.n_steps; ++s) {
-        const unsigned flag = a.flag0 + (unsigned)s + 1u;
+        const long long mb_next = wrap(mb + a.B);
         float4 g[CH];
 #pragma unroll
         for (int ch = 0; ch < CH; ++ch) g[ch] = make_float4(0.f, 0.f, 0.f, 0.f);
         float loss_acc = 0.f;
+        if (tid == 0) dbg_stamp(a, s, 0);
+        // a CTA without rows still takes part in every exchange
+        if (nsb == 0 && s > 0) {
+            mbar_wait(smem_u32(wfull), (uint32_t)(s - 1) & 1u, a.err);
+            apply_total(s - 1);
+        }
 
         for (int sb = 0; sb < nsb; ++sb) {
-            // label of the row this lane finishes (issued early: the latency hides
-            // behind the shared-memory waits below)
-            const int iy = sb * rows_per_sb + ridx * RG + rg;
-            const bool vy = active && iy < nrows_c;
-            float yv = 0.f;
-            if (vy) yv = __ldg(a.y + (size_t)((mb + lo + iy) % a.n_rows));
-
+            const int j = sb * RG + rg;               // this group's stage of the step
+            const bool have = active && j < nst_c;    // warp-uniform
+            const int rc = have ? min(R, nrows_c - j * R) : 0;
+            const float yv = y_next;
+            {   // prefetch the label for this group's next stage (maybe next step's first)
+                if (sb + 1 < nsb) y_next = load_y(mb, j + RG);
+                else y_next = (s + 1 < a.n_steps) ? load_y(mb_next, rg) : 0.f;
+            }
             float4 x[R][CH];
+            if (have) {
+                uint32_t sl = base_slot + (uint32_t)(j * SPB);
+                uint32_t k = sl / (uint32_t)ns;
+                uint32_t slot = sl - k * (uint32_t)ns;
+                uint32_t par = (base_phase ^ k) & 1u;
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const int i = sb * rows_per_sb + r * RG + rg;
-                if (active && i < nrows_c) {  // warp-uniform
-                    const uint32_t sl = base_slot + (uint32_t)i;
-                    const uint32_t k = sl / (uint32_t)ns;
-                    const uint32_t slot = sl - k * (uint32_t)ns;
-                    mbar_wait(smem_u32(&full[slot]), (base_phase ^ k) & 1u, a.err);
-                    const uint32_t rb = smem_u32(ring + (size_t)slot * row_bytes);
+                for (int q = 0; q < SPB; ++q) {
+                    if (q * RS < rc) {  // warp-uniform
+                        mbar_wait(smem_u32(&full[slot]), par, a.err);
+                        const uint32_t sbase = smem_u32(ring + (size_t)slot * slot_bytes);
 #pragma unroll
-                    for (int ch = 0; ch < CH; ++ch)
-                        x[r][ch] = gv[ch] ? lds_v4(rb + (uint32_t)gq[ch] * 16u)
-                                          : make_float4(0.f, 0.f, 0.f, 0.f);
-                } else {
+                        for (int rr = 0; rr < RS; ++rr) {
+                            const int r = q * RS + rr;
+#pragma unroll
+                            for (int ch = 0; ch < CH; ++ch)
+                                x[r][ch] = (gv[ch] && r < rc)
+                                               ? lds_v4(sbase + (uint32_t)rr * (uint32_t)row_bytes +
+                                                        (uint32_t)gq[ch] * 16u)
+                                               : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(&empty[slot]));  // rows are in registers
+                        if (++slot == (uint32_t)ns) { slot = 0; par ^= 1u; }
+                    } else {
+#pragma unroll
+                        for (int rr = 0; rr < RS; ++rr)
+#pragma unroll
+                            for (int ch = 0; ch < CH; ++ch)
+                                x[q * RS + rr][ch] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r)
 #pragma unroll
                     for (int ch = 0; ch < CH; ++ch) x[r][ch] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
+            }
+            if (sb == 0 && s > 0) {
+                // the rows of the step's first stage are already in registers: only now
+                // wait for the previous step's gradient total and update the weights
+                mbar_wait(smem_u32(wfull), (uint32_t)(s - 1) & 1u, a.err);
+                apply_total(s - 1);
+                if (tid == 0) dbg_stamp(a, s, 5);
             }
             // partial dot products over this thread's columns
             float d[R];
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                float acc = 0.f;
+            for (int r = 0; r < R; ++r) d[r] = 0.f;
 #pragma unroll
-                for (int ch = 0; ch < CH; ++ch) {
-                    acc = fmaf(x[r][ch].x, w[ch].x, acc);
-                    acc = fmaf(x[r][ch].y, w[ch].y, acc);
-                    acc = fmaf(x[r][ch].z, w[ch].z, acc);
-                    acc = fmaf(x[r][ch].w, w[ch].w, acc);
+            for (int ch = 0; ch < CH; ++ch) {
+                float4 wv;
+                if (WS) wv = gv[ch] ? lds_v4(wsm_a + (uint32_t)gq[ch] * 16u)
+                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+                else wv = w[ch];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    float acc = d[r];
+                    acc = fmaf(x[r][ch].x, wv.x, acc);
+                    acc = fmaf(x[r][ch].y, wv.y, acc);
+                    acc = fmaf(x[r][ch].z, wv.z, acc);
+                    acc = fmaf(x[r][ch].w, wv.w, acc);
+                    d[r] = acc;
                 }
-                d[r] = acc;
             }
             MultiReduce<R, 16>::run(d, lane);
             float z = d[0];  // warp total for row ridx
@@ -358,22 +619,8 @@ __global__ void __launch_bounds__(NCW * 32, 1) lr_persist_kernel(const LrArgs a)
                 for (int k = 0; k < WPG; ++k) z += rb[(rg * WPG + k) * R + ridx];
                 red_buf ^= 1;
             }
-            // Every warp of the group has its rows in registers (the dot products above
-            // consumed them, and for WPG > 1 the barrier was passed): re-arm the slots
-            // with the rows NS positions further down this CTA's stream.
-            if (leader) {
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#pragma unroll 1
-                for (int r = 0; r < R; ++r) {
-                    const int i = sb * rows_per_sb + r * RG + rg;
-                    if (i < nrows_c) {
-                        const long long nxt = (long long)s * nrows_c + i + ns;
-                        if (nxt < total_rows) issue_row(nxt);
-                    }
-                }
-            }
             float resid = 0.f;
-            if (vy) {
+            if (ridx < rc) {
                 resid = sigmoid_f(z) - yv;
                 if (canon && wig == 0) loss_acc += softplus_f(z) - yv * z;
             }
@@ -389,14 +636,15 @@ __global__ void __launch_bounds__(NCW * 32, 1) lr_persist_kernel(const LrArgs a)
                 }
             }
         }
-        {   // advance the ring cursor past this step's rows
-            const uint32_t sl = base_slot + (uint32_t)nrows_c;
+        {   // advance the ring cursor past this step's slots
+            const uint32_t sl = base_slot + (uint32_t)nsl_c;
             const uint32_t k = sl / (uint32_t)ns;
             base_slot = sl - k * (uint32_t)ns;
             base_phase ^= (k & 1u);
         }
+        if (tid == 0) dbg_stamp(a, s, 1);
 
-        // ---- combine row groups inside the CTA, publish this CTA's partial ----------
+        // ---- combine row groups inside the CTA, hand the CTA's gradient to the exchange ----
         if (active && wig == 0) {
             const float l = warp_sum(loss_acc);
             if (lane == 0) lsm[rg] = l;
@@ -410,13 +658,14 @@ __global__ void __launch_bounds__(NCW * 32, 1) lr_persist_kernel(const LrArgs a)
             }
             named_bar_sync(1, NCT);
         }
-        uint4* mine = a.part_ll + (size_t)c * a.Q;
-        if (tid == 0) {
-            float l = 0.f;
-            for (int k = 0; k < RG; ++k) l += lsm[k];
-            st_vol_v4(mine + (a.Q - 1), make_uint4(__float_as_uint(l), flag, 0u, flag));
-        }
         if (rg == 0) {
+            unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
+            if (tid == 0) {
+                float l = 0.f;
+                for (int k = 0; k < RG; ++k) l += lsm[k];
+                if (XB) { gout[F] = to_fix(l); gout[F + 1] = 0; }
+                else red_add_u64(buf + F, (unsigned long long)to_fix(l));
+            }
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch) {
                 if (!gv[ch]) continue;
@@ -426,87 +675,46 @@ __global__ void __launch_bounds__(NCW * 32, 1) lr_persist_kernel(const LrArgs a)
                         *reinterpret_cast<const float4*>(gsm + (size_t)(k - 1) * F + gq[ch] * 4);
                     t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w;
                 }
-                st_vol_v4(mine + 2 * gq[ch],
-                          make_uint4(__float_as_uint(t.x), flag, __float_as_uint(t.y), flag));
-                st_vol_v4(mine + 2 * gq[ch] + 1,
-                          make_uint4(__float_as_uint(t.z), flag, __float_as_uint(t.w), flag));
-            }
-        }
-
-        // ---- owner: sum the packets of every CTA in a fixed order, update, publish ----
-        for (int q = q0 + warp; q < q1; q += NCW) {
-            double a0 = 0.0, a1 = 0.0;
-            for (int sbase = 0; sbase < G; sbase += 128) {
-                uint4 p[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int src = sbase + k * 32 + lane;
-                    if (src < G) p[k] = ld_vol_v4(a.part_ll + (size_t)src * a.Q + q);
-                }
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int src = sbase + k * 32 + lane;
-                    if (src < G) {
-                        uint32_t spins = 0;
-                        while (p[k].y != flag || p[k].w != flag) {
-                            if (spin_abort(spins, a.err, kErrTimeoutPart)) break;
-                            p[k] = ld_vol_v4(a.part_ll + (size_t)src * a.Q + q);
-                        }
-                        a0 += (double)__uint_as_float(p[k].x);
-                        a1 += (double)__uint_as_float(p[k].z);
-                    }
-                }
-            }
-            a0 = warp_sum(a0);
-            a1 = warp_sum(a1);
-            if (lane == 0) {
-                if (q == a.Q - 1) {
-                    if (a.loss_out) a.loss_out[s] = a0 / (double)a.B;
+                if (XB) {
+                    longlong2* p = reinterpret_cast<longlong2*>(gout + gq[ch] * 4);
+                    p[0] = make_longlong2(to_fix(t.x), to_fix(t.y));
+                    p[1] = make_longlong2(to_fix(t.z), to_fix(t.w));
                 } else {
-                    const int i = 2 * (q - q0);
-                    const double w0 = own_w[i] - a.eta_over_b * a0;
-                    const double w1 = own_w[i + 1] - a.eta_over_b * a1;
-                    own_w[i] = w0;
-                    own_w[i + 1] = w1;
-                    st_vol_v4(a.w_ll + q, make_uint4(__float_as_uint((float)w0), flag,
-                                                     __float_as_uint((float)w1), flag));
+                    red_add_u64(buf + gq[ch] * 4 + 0, (unsigned long long)to_fix(t.x));
+                    red_add_u64(buf + gq[ch] * 4 + 1, (unsigned long long)to_fix(t.y));
+                    red_add_u64(buf + gq[ch] * 4 + 2, (unsigned long long)to_fix(t.z));
+                    red_add_u64(buf + gq[ch] * 4 + 3, (unsigned long long)to_fix(t.w));
                 }
             }
+            if (XB) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(gfull));
+            } else {
+                __threadfence();  // this thread's adds are performed before the CTA signals
+                mbar_arrive(smem_u32(gfull));
+            }
         }
-
-        // ---- everybody: pick up the new weights ------------------------------------
-        if (s + 1 < a.n_steps) {
-            uint4 p[CH][2];
-#pragma unroll
-            for (int ch = 0; ch < CH; ++ch)
-                if (gv[ch]) {
-                    p[ch][0] = ld_vol_v4(a.w_ll + 2 * gq[ch]);
-                    p[ch][1] = ld_vol_v4(a.w_ll + 2 * gq[ch] + 1);
-                }
-#pragma unroll
-            for (int ch = 0; ch < CH; ++ch)
-                if (gv[ch]) {
-#pragma unroll
-                    for (int hh = 0; hh < 2; ++hh) {
-                        uint32_t spins = 0;
-                        while (p[ch][hh].y != flag || p[ch][hh].w != flag) {
-                            if (spin_abort(spins, a.err, kErrTimeoutW)) break;
-                            p[ch][hh] = ld_vol_v4(a.w_ll + 2 * gq[ch] + hh);
-                        }
-                    }
-                    w[ch] = make_float4(__uint_as_float(p[ch][0].x), __uint_as_float(p[ch][0].z),
-                                        __uint_as_float(p[ch][1].x), __uint_as_float(p[ch][1].z));
-                }
-            mb = (mb + a.B) % a.n_rows;
-        }
+        if (tid == 0) dbg_stamp(a, s, 2);
+        mb = mb_next;
     }
 
-    // master weights back to global (each packet's owner lane wrote own_w itself)
-    for (int q = q0 + warp; q < q1; q += NCW) {
-        if (lane == 0 && q < a.Q - 1) {
-            const int i = 2 * (q - q0);
-            a.model[2 * q] = own_w[i];
-            a.model[2 * q + 1] = own_w[i + 1];
+    // the last step's total
+    if (a.n_steps > 0) {
+        mbar_wait(smem_u32(wfull), (uint32_t)(a.n_steps - 1) & 1u, a.err);
+        apply_total(a.n_steps - 1);
+    }
+    // master weights back to global: all CTAs hold identical copies, CTA 0 writes
+    if (c == 0 && rg == 0) {
+#pragma unroll
+        for (int ch = 0; ch < CH; ++ch) {
+            if (!gv[ch]) continue;
+            double* m = a.model + gq[ch] * 4;
+            if (WS) {
+                const double* mm = my_master + gq[ch] * 4;
+                m[0] = mm[0]; m[1] = mm[1]; m[2] = mm[2]; m[3] = mm[3];
+            } else {
+                m[0] = wm[ch][0]; m[1] = wm[ch][1]; m[2] = wm[ch][2]; m[3] = wm[ch][3];
+            }
         }
     }
 }

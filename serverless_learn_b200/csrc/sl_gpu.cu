@@ -69,19 +69,24 @@ const char* load_nccl() {
 
 // ---- persistent-kernel variants -----------------------------------------------------
 struct Variant {
-    int ch, r, ncw;
+    int ch, r, rs, ncw, xb, ws;
     const void* fn;
 };
-#define SL_VARIANT(CH, R, NCW) \
-    Variant { CH, R, NCW, (const void*)slk::lr_persist_kernel<CH, R, NCW> }
+#define SL_VARIANT(CH, R, RS, NCW, XB, WS) \
+    Variant { CH, R, RS, NCW, XB, WS, \
+              (const void*)slk::lr_persist_kernel<CH, R, RS, NCW, (XB) != 0, (WS) != 0> }
+// auto-selection takes the first variant wide enough for F
 const Variant kVariants[] = {
-    SL_VARIANT(1, 16, 16),  // 1: F <= 2048, 32 rows per sub-batch at F = 1024
-    SL_VARIANT(1, 8, 16),   // 2
-    SL_VARIANT(1, 32, 8),   // 3: F <= 1024, 8 consumer warps
-    SL_VARIANT(2, 8, 16),   // 4: F <= 4096
-    SL_VARIANT(4, 4, 16),   // 5: F <= 8192
-    SL_VARIANT(8, 2, 8),    // 6: F <= 8192, 8 warps
-    SL_VARIANT(16, 1, 8),   // 7: F <= 16384
+    SL_VARIANT(1, 32, 4, 8, 1, 0),    // 1: F <= 1024; a CTA's 28 rows of a step in one sub-batch
+    SL_VARIANT(1, 16, 4, 16, 1, 0),   // 2: F <= 2048; two row groups of 16 rows
+    SL_VARIANT(1, 16, 4, 8, 1, 0),    // 3: F <= 1024
+    SL_VARIANT(1, 8, 4, 16, 1, 0),    // 4: F <= 2048
+    SL_VARIANT(2, 8, 4, 8, 1, 0),     // 5: F <= 2048
+    SL_VARIANT(4, 4, 2, 8, 1, 0),     // 6: F <= 4096
+    SL_VARIANT(4, 4, 2, 16, 0, 0),    // 7: F <= 8192, per-element exchange
+    SL_VARIANT(8, 1, 1, 16, 0, 1),    // 8: F <= 16384, weights in shared memory
+    SL_VARIANT(8, 2, 1, 8, 0, 1),     // 9: F <= 8192,  weights in shared memory
+    SL_VARIANT(1, 16, 4, 8, 0, 0),    // 10: as 3 with the per-element exchange
 };
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
@@ -114,10 +119,11 @@ struct sl_handle {
 
     // training scratch
     long long step = 0;
-    unsigned flag_base = 0;
-    uint4 *part_ll = nullptr, *w_ll = nullptr;
-    size_t part_ll_bytes = 0;
-    int ll_grid = 0;
+    unsigned long long* acc = nullptr;   // [3][krep][Fp] gradient accumulators
+    size_t acc_bytes = 0;
+    unsigned* counter = nullptr;
+    double* wmaster = nullptr;           // [grid][F] (wide-row variants)
+    size_t wmaster_bytes = 0;
     double* d_loss = nullptr;
     double* h_loss = nullptr;
     size_t loss_cap = 0;
@@ -127,6 +133,9 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
+    long long opt_dbg_step = -1, opt_ring = 0;
+    unsigned long long* dbg = nullptr;
+    size_t dbg_words = 0;
     // info
     long long launches = 0, path_used = 0, variant_used = 0, grid_used = 0, ns_used = 0,
               smem_used = 0;
@@ -257,65 +266,82 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     memset(&a, 0, sizeof(a));
     a.F = F;
     a.B = h->B;
-    a.Q = F / 2 + 1;
-    a.qpc = (a.Q + grid - 1) / grid;
+    a.Fp = F + 2;
+    a.krep = !v.xb ? 1 : (F <= 1024 ? 4 : (F <= 2048 ? 2 : 1));
     a.wpg = (granules + v.ch * 32 - 1) / (v.ch * 32);
     a.row_bytes = 4 * F;
     const int rg = v.ncw / a.wpg;
     // fixed shared-memory regions after the ring
     const size_t red_b = sizeof(float) * 2 * v.ncw * v.r;
     const size_t lsm_b = sizeof(float) * v.ncw;
-    const size_t own_b = sizeof(double) * 2 * a.qpc;
     const size_t gsm_b = sizeof(float) * (size_t)std::max(0, rg - 1) * F;
-    const size_t fixed = red_b + lsm_b + own_b + gsm_b + 256;
-    if (h->smem_optin < fixed + 16 + (size_t)a.row_bytes) {
-        *why = "row does not fit in shared memory";
+    const size_t gout_b = v.xb ? 8 * (size_t)a.Fp : 0;
+    const size_t gin_b = v.xb ? 8 * (size_t)a.Fp * a.krep : 0;
+    const size_t wsm_b = v.ws ? sizeof(float) * (size_t)F : 0;
+    const size_t fixed = red_b + lsm_b + gsm_b + gout_b + gin_b + wsm_b + 512;
+    const size_t slot_b = (size_t)v.rs * a.row_bytes;
+    if (slot_b > (1u << 20) - 16 || h->smem_optin < fixed + 16 + slot_b) {
+        *why = "a ring slot does not fit in shared memory";
         return false;
     }
-    size_t ns = (h->smem_optin - fixed) / ((size_t)a.row_bytes + 8);
-    ns = std::min<size_t>(ns, 1024);
+    size_t ns = (h->smem_optin - fixed) / (slot_b + 16);
+    ns = std::min<size_t>(ns, 256);
+    if (h->opt_ring > 0) ns = std::min<size_t>(ns, (size_t)h->opt_ring);
     if (ns < 1) { *why = "no ring slot fits"; return false; }
     a.ns = (int)ns;
-    size_t off = (size_t)a.ns * a.row_bytes;
-    off = align_up(off, 16); a.off_full = (int)off;  off += 8 * ns;
+    size_t off = (size_t)a.ns * slot_b;
+    off = align_up(off, 16); a.off_bar = (int)off;   off += 8 * (2 * ns + 2);
     off = align_up(off, 16); a.off_red = (int)off;   off += red_b;
     a.off_lsm = (int)off;                            off += lsm_b;
-    off = align_up(off, 16); a.off_own = (int)off;   off += own_b;
     off = align_up(off, 16); a.off_gsm = (int)off;   off += gsm_b;
+    off = align_up(off, 128); a.off_gout = (int)off; off += gout_b;
+    off = align_up(off, 128); a.off_gin = (int)off;  off += gin_b;
+    off = align_up(off, 16); a.off_wsm = (int)off;   off += wsm_b;
     p->smem = off;
     p->variant = vi;
     p->grid = grid;
     return true;
 }
 
-int ensure_ll(sl_handle* h, int grid, int Q) {
-    const size_t need = sizeof(uint4) * (size_t)grid * Q;
-    if (h->part_ll && h->part_ll_bytes >= need && h->ll_grid == grid) return SL_OK;
-    if (h->part_ll) cudaFree(h->part_ll);
-    if (h->w_ll) cudaFree(h->w_ll);
-    h->part_ll = nullptr;
-    h->w_ll = nullptr;
-    CK(h, cudaMalloc(&h->part_ll, need));
-    CK(h, cudaMalloc(&h->w_ll, sizeof(uint4) * Q));
-    // flag 0 is never expected first (flags start at flag_base + 1 >= 1)
-    CK(h, cudaMemsetAsync(h->part_ll, 0, need, h->stream));
-    CK(h, cudaMemsetAsync(h->w_ll, 0, sizeof(uint4) * Q, h->stream));
-    h->part_ll_bytes = need;
-    h->ll_grid = grid;
-    h->flag_base = 0;
+int ensure_exchange(sl_handle* h, const PersistPlan& plan) {
+    const Variant& v = kVariants[plan.variant];
+    const size_t need = 8 * (size_t)3 * plan.args.krep * plan.args.Fp;
+    if (h->acc_bytes < need) {
+        if (h->acc) cudaFree(h->acc);
+        h->acc = nullptr;
+        h->acc_bytes = 0;
+        CK(h, cudaMalloc(&h->acc, need));
+        h->acc_bytes = need;
+    }
+    if (!h->counter) CK(h, cudaMalloc(&h->counter, 256));
+    if (v.ws) {
+        const size_t wb = sizeof(double) * (size_t)plan.grid * h->F;
+        if (h->wmaster_bytes < wb) {
+            if (h->wmaster) cudaFree(h->wmaster);
+            h->wmaster = nullptr;
+            h->wmaster_bytes = 0;
+            CK(h, cudaMalloc(&h->wmaster, wb));
+            h->wmaster_bytes = wb;
+        }
+    }
     return SL_OK;
 }
 
 int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_loss) {
     const Variant& v = kVariants[plan.variant];
-    int rc = ensure_ll(h, plan.grid, plan.args.Q);
+    int rc = ensure_exchange(h, plan);
     if (rc) return rc;
     CK(h, cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
     int occ = 0;
-    CK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, v.ncw * 32, plan.smem));
+    CK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, (v.ncw + 2) * 32, plan.smem));
     if (occ < 1) return fail(h, SL_ECUDA, "persistent kernel does not fit on an SM");
-    const int max_per_launch =
+    int max_per_launch =
         h->opt_steps_per_launch > 0 ? (int)h->opt_steps_per_launch : kMaxStepsPerLaunch;
+    {   // the kernel counts its streamed rows in 32 bits
+        const long long rows_per_cta = (h->B + plan.grid - 1) / plan.grid;  // >= stages per CTA
+        const long long cap = ((1ll << 31) - 1 - plan.args.ns) / std::max(1ll, rows_per_cta);
+        max_per_launch = (int)std::max(1ll, std::min<long long>(max_per_launch, cap));
+    }
     int done = 0;
     *h->h_err = 0;
     while (done < n_steps) {
@@ -329,18 +355,34 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         a.step0 = h->step;
         a.n_steps = n;
         a.model = h->model;
-        a.part_ll = h->part_ll;
-        a.w_ll = h->w_ll;
+        a.acc = h->acc;
+        a.counter = h->counter;
+        a.wmaster = h->wmaster;
         a.loss_out = want_loss ? h->d_loss + done : nullptr;
-        a.flag0 = h->flag_base;
+        // accumulators and the arrival counter start every launch at zero
+        CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
+        CK(h, cudaMemsetAsync(h->counter, 0, 4, h->stream));
         a.eta_over_b = h->eta / (double)h->B;
         a.err = h->d_err;
+        a.dbg = nullptr;
+        a.dbg_step = 0;
+        if (h->opt_dbg_step >= 0 && done == 0) {
+            const size_t words = (size_t)4 * plan.grid * 16;
+            if (h->dbg_words < words) {
+                if (h->dbg) cudaFree(h->dbg);
+                h->dbg = nullptr;
+                CK(h, cudaMalloc(&h->dbg, words * 8));
+                h->dbg_words = words;
+            }
+            CK(h, cudaMemsetAsync(h->dbg, 0, words * 8, h->stream));
+            a.dbg = h->dbg;
+            a.dbg_step = (int)h->opt_dbg_step;
+        }
         void* params[] = {&a};
-        CK(h, cudaLaunchCooperativeKernel(v.fn, dim3(plan.grid), dim3(v.ncw * 32), params,
+        CK(h, cudaLaunchCooperativeKernel(v.fn, dim3(plan.grid), dim3((v.ncw + 2) * 32), params,
                                           plan.smem, h->stream));
         h->launches++;
         h->step += n;
-        h->flag_base += (unsigned)n;
         done += n;
     }
     h->path_used = 1;
@@ -505,7 +547,8 @@ int sl_destroy(sl_handle* h) {
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->model); cudaFree(h->old); cudaFree(h->shard);
-    cudaFree(h->part_ll); cudaFree(h->w_ll); cudaFree(h->d_loss);
+    cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->d_loss);
+    cudaFree(h->dbg);
     cudaFree(h->resid); cudaFree(h->rowloss); cudaFree(h->gpart); cudaFree(h->gsum);
     if (h->h_in) cudaFreeHost(h->h_in);
     if (h->h_out) cudaFreeHost(h->h_out);
@@ -535,6 +578,8 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "path") h->opt_path = value;  // 0 auto, 1 persistent only, 2 simple
     else if (k == "steps_per_launch") h->opt_steps_per_launch = value;
     else if (k == "step") h->step = value;
+    else if (k == "debug_timeline") h->opt_dbg_step = value;
+    else if (k == "ring_slots") h->opt_ring = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
 }
@@ -652,6 +697,15 @@ int sl_shard_read(sl_handle* h, size_t offset, void* out, size_t n) {
     DeviceGuard dg(h->device);
     CK(h, cudaMemcpyAsync(out, h->shard + offset, n, cudaMemcpyDeviceToHost, h->stream));
     CK(h, cudaStreamSynchronize(h->stream));
+    return SL_OK;
+}
+
+int sl_debug_read(sl_handle* h, unsigned long long* out, size_t n_words) {
+    if (!h || !out) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->dbg || n_words > h->dbg_words) return fail(h, SL_ESTATE, "no debug timeline recorded");
+    DeviceGuard dg(h->device);
+    CK(h, cudaMemcpy(out, h->dbg, n_words * 8, cudaMemcpyDeviceToHost));
     return SL_OK;
 }
 

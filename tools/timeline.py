@@ -1,0 +1,39 @@
+"""Per-step timeline of the persistent kernel (diagnostic): python tools/timeline.py [variant]"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from serverless_learn_b200 import Replica  # noqa: E402
+
+variant = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+F = 1024
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+with Replica(F, B) as r:
+    r.shard_synth(1 << 20)
+    r.set_option("variant", variant)
+    r.train_steps(64, want_loss=False)
+    r.set_option("debug_timeline", 100)
+    r.train_steps(256, want_loss=False)
+    G = r.info("grid")
+    buf = np.zeros(4 * G * 16, dtype=np.uint64)
+    rc = r._L.sl_debug_read(r._h, buf.ctypes.data_as(C.POINTER(C.c_ulonglong)), buf.size)
+    assert rc == 0
+    t = buf.reshape(4, G, 8, 2).astype(np.int64)
+names = ["P0 step start", "P1 compute done", "P2 partial stored", "P3 owner done", "P4 w received", "P5 first rows in regs"]
+order = [0, 5, 1, 2, 3, 4]
+for s in range(1, 3):
+    g0 = t[s, :, 0, 1].min()
+    print(f"--- step {100 + s}: globaltimer ns relative to earliest CTA step start (min / median / max over CTAs)")
+    for p in order:
+        v = t[s, :, p, 1] - g0
+        print(f"  {names[p]:24s} {v.min():7d} {int(np.median(v)):7d} {v.max():7d}")
+    ck = t[s, :, :, 0]
+    print("  SM-clock deltas (median over CTAs): " + ", ".join(
+        f"{names[b][:2]}-{names[a][:2]}={int(np.median(ck[:, b] - ck[:, a]))}" for a, b in [(0, 5), (5, 1), (1, 2), (2, 3), (3, 4)]))
+    nxt = t[s + 1, :, 0, 1] - g0
+    print(f"  next step start          {nxt.min():7d} {int(np.median(nxt)):7d} {nxt.max():7d}")
+    late = np.argsort(-(t[s, :, 2, 1] - g0))[:5]
+    print("  latest P2 CTAs:", late.tolist(), (t[s, late, 2, 1] - g0).tolist())
