@@ -245,16 +245,17 @@ struct LrArgs {
     unsigned long long* acc;   // [3][krep][Fp] s64 gradient accumulators (zero at launch)
     unsigned* counter;     // arrivals; zero at launch
     double* wmaster;       // WS only: [grid][F] per-CTA fp64 master copies
-    double* loss_out;      // device [n_steps] or nullptr
+    unsigned long long* loss_fix;  // device [n_steps] s64 fixed-point loss sums (zero at launch) or nullptr
     double eta_over_b;
     int* err;              // 0 = ok; set by the watchdog
     // geometry, computed on the host
-    int Fp;                // padded vector length: F + 2 (element F carries the loss)
+    int Fp;                // accumulator vector length (= F)
+    int zy_rows;           // rows of the deferred-loss buffer (>= this CTA's rows per step)
     int krep;              // accumulator replicas
     int wpg;               // warps per row group = ceil(F/4/CH/32)
     int ns;                // ring slots (RS rows each)
     int row_bytes;         // 4*F
-    int off_bar, off_red, off_lsm, off_gsm, off_gout, off_gin, off_wsm;  // smem offsets
+    int off_bar, off_red, off_zy, off_gsm, off_gout, off_gin, off_wsm;  // smem offsets
     // diagnostics (sl_set_option "debug_timeline"): [4 steps][grid][16] time stamps
     unsigned long long* dbg;
     int dbg_step;
@@ -298,7 +299,8 @@ __device__ __forceinline__ void red_release_add_u32(unsigned* p, unsigned v) {
 __device__ __forceinline__ void red_add_u64(unsigned long long* p, unsigned long long v) {
     asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ long long to_fix(float v) { return __double2ll_rn((double)v * kFixScale); }
+// exact: scaling by 2^36 does not round in fp32, the conversion rounds once
+__device__ __forceinline__ long long to_fix(float v) { return __float2ll_rn(v * 68719476736.0f); }
 
 template <int CH, int R, int RS, int NCW, bool XB, bool WS>
 __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrArgs a) {
@@ -314,7 +316,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     uint64_t* gfull = empty + a.ns;                                    // [1] gradient staged
     uint64_t* wfull = gfull + 1;                                       // [1] total received
     float* red = reinterpret_cast<float*>(smem + a.off_red);          // [2][NCW][R]
-    float* lsm = reinterpret_cast<float*>(smem + a.off_lsm);          // [NCW]
+    float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);          // [2][zy_rows] (z, y) per row
     float* gsm = reinterpret_cast<float*>(smem + a.off_gsm);          // [RG-1][F]
     long long* gout = reinterpret_cast<long long*>(smem + a.off_gout);  // XB: [Fp]
     long long* gin = reinterpret_cast<long long*>(smem + a.off_gin);    // XB: [krep][Fp]
@@ -389,12 +391,14 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             // the CTA's gradient is staged (XB) or has been added by the compute threads
             mbar_wait(smem_u32(gfull), (uint32_t)s & 1u, a.err);
             if (lane == 0) {
+                dbg_stamp(a, s, 6);
                 if (XB) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     bulk_reduce_add_u64(buf + (size_t)(c % KREP) * Fp, smem_u32(gout),
                                         (uint32_t)Fp * 8u);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+                    dbg_stamp(a, s, 7);
                     asm volatile("fence.proxy.async;" ::: "memory");
                 }
                 red_release_add_u32(a.counter, 1u);
@@ -503,12 +507,6 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                 w[ch] = make_float4((float)wm[ch][0], (float)wm[ch][1], (float)wm[ch][2], (float)wm[ch][3]);
             }
         }
-        if (c == 0 && tid == 0 && a.loss_out) {
-            long long l = 0;
-            if (XB) for (int k = 0; k < KREP; ++k) l += gin[(size_t)k * Fp + F];
-            else l = (long long)ld_relaxed_u64(buf + F);
-            a.loss_out[s] = ((double)l * kFixInv) / (double)a.B;
-        }
         if (WS && RG > 1) named_bar_sync(1, NCT);  // other groups read rg 0's smem weights
     };
 
@@ -527,7 +525,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         float4 g[CH];
 #pragma unroll
         for (int ch = 0; ch < CH; ++ch) g[ch] = make_float4(0.f, 0.f, 0.f, 0.f);
-        float loss_acc = 0.f;
+        float2* zyb = zy + (size_t)(s & 1) * a.zy_rows;
         if (tid == 0) dbg_stamp(a, s, 0);
         // a CTA without rows still takes part in every exchange
         if (nsb == 0 && s > 0) {
@@ -622,7 +620,8 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             float resid = 0.f;
             if (ridx < rc) {
                 resid = sigmoid_f(z) - yv;
-                if (canon && wig == 0) loss_acc += softplus_f(z) - yv * z;
+                // the loss is evaluated after the gradient has been handed off
+                if (canon && wig == 0 && a.loss_fix) zyb[j * R + ridx] = make_float2(z, yv);
             }
 #pragma unroll
             for (int r = 0; r < R; ++r) {
@@ -645,10 +644,6 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         if (tid == 0) dbg_stamp(a, s, 1);
 
         // ---- combine row groups inside the CTA, hand the CTA's gradient to the exchange ----
-        if (active && wig == 0) {
-            const float l = warp_sum(loss_acc);
-            if (lane == 0) lsm[rg] = l;
-        }
         if (RG > 1) {
             if (active && rg > 0) {
 #pragma unroll
@@ -660,12 +655,6 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         }
         if (rg == 0) {
             unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
-            if (tid == 0) {
-                float l = 0.f;
-                for (int k = 0; k < RG; ++k) l += lsm[k];
-                if (XB) { gout[F] = to_fix(l); gout[F + 1] = 0; }
-                else red_add_u64(buf + F, (unsigned long long)to_fix(l));
-            }
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch) {
                 if (!gv[ch]) continue;
@@ -695,6 +684,16 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             }
         }
         if (tid == 0) dbg_stamp(a, s, 2);
+        // off the critical path (the exchange is in flight): this step's loss
+        if (warp == 0 && a.loss_fix) {
+            float l = 0.f;
+            for (int i = lane; i < nrows_c; i += 32) {
+                const float2 v = zyb[i];
+                l += softplus_f(v.x) - v.y * v.x;
+            }
+            l = warp_sum(l);
+            if (lane == 0) red_add_u64(a.loss_fix + s, (unsigned long long)to_fix(l));
+        }
         mb = mb_next;
     }
 
@@ -806,6 +805,12 @@ __global__ void __launch_bounds__(256) lr_finish_kernel(const float* __restrict_
             else gsum[F] = sm[0];
         }
     }
+}
+
+__global__ void loss_finish_kernel(const unsigned long long* __restrict__ fix, double* __restrict__ out,
+                                   int n, double inv_b) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = ((double)(long long)fix[i] * kFixInv) * inv_b;
 }
 
 // after the all-reduce of gsum[F+1] over nranks: model -= eta/(B*nranks) * gsum

@@ -77,17 +77,18 @@ struct Variant {
               (const void*)slk::lr_persist_kernel<CH, R, RS, NCW, (XB) != 0, (WS) != 0> }
 // auto-selection takes the first variant wide enough for F
 const Variant kVariants[] = {
-    SL_VARIANT(1, 32, 4, 8, 1, 0),    // 1: F <= 1024; a CTA's 28 rows of a step in one sub-batch
+    SL_VARIANT(1, 16, 4, 8, 1, 0),    // 1: F <= 1024; measured best at F=1024, B/grid = 28
     SL_VARIANT(1, 16, 4, 16, 1, 0),   // 2: F <= 2048; two row groups of 16 rows
-    SL_VARIANT(1, 16, 4, 8, 1, 0),    // 3: F <= 1024
+    SL_VARIANT(1, 32, 4, 8, 1, 0),    // 3: F <= 1024; a CTA's 28 rows of a step in one sub-batch
     SL_VARIANT(1, 8, 4, 16, 1, 0),    // 4: F <= 2048
     SL_VARIANT(2, 8, 4, 8, 1, 0),     // 5: F <= 2048
     SL_VARIANT(4, 4, 2, 8, 1, 0),     // 6: F <= 4096
     SL_VARIANT(4, 4, 2, 16, 0, 0),    // 7: F <= 8192, per-element exchange
     SL_VARIANT(8, 1, 1, 16, 0, 1),    // 8: F <= 16384, weights in shared memory
     SL_VARIANT(8, 2, 1, 8, 0, 1),     // 9: F <= 8192,  weights in shared memory
-    SL_VARIANT(1, 16, 4, 8, 0, 0),    // 10: as 3 with the per-element exchange
+    SL_VARIANT(4, 4, 4, 14, 1, 0),    // 10: F <= 1024 as 7 row groups of 2 warps x 4 rows
 };
+
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 }  // namespace
@@ -133,7 +134,8 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0;
+    unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
     size_t dbg_words = 0;
     // info
@@ -219,12 +221,15 @@ int ensure_simple_scratch(sl_handle* h) {
 int ensure_loss_cap(sl_handle* h, size_t n) {
     if (n <= h->loss_cap) return SL_OK;
     if (h->d_loss) cudaFree(h->d_loss);
+    if (h->loss_fix) cudaFree(h->loss_fix);
+    h->loss_fix = nullptr;
     if (h->h_loss) cudaFreeHost(h->h_loss);
     h->d_loss = nullptr;
     h->h_loss = nullptr;
     h->loss_cap = 0;
     size_t cap = std::max<size_t>(n, 1024);
     CK(h, cudaMalloc(&h->d_loss, sizeof(double) * cap));
+    CK(h, cudaMalloc(&h->loss_fix, 8 * cap));
     CK(h, cudaMallocHost(&h->h_loss, sizeof(double) * cap));
     h->loss_cap = cap;
     return SL_OK;
@@ -266,19 +271,21 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     memset(&a, 0, sizeof(a));
     a.F = F;
     a.B = h->B;
-    a.Fp = F + 2;
+    a.Fp = F;
+    a.zy_rows = (((h->B + grid - 1) / grid + v.r - 1) / v.r) * v.r;
     a.krep = !v.xb ? 1 : (F <= 1024 ? 4 : (F <= 2048 ? 2 : 1));
+    if (v.xb && h->opt_krep > 0) a.krep = (int)h->opt_krep;
     a.wpg = (granules + v.ch * 32 - 1) / (v.ch * 32);
     a.row_bytes = 4 * F;
     const int rg = v.ncw / a.wpg;
     // fixed shared-memory regions after the ring
     const size_t red_b = sizeof(float) * 2 * v.ncw * v.r;
-    const size_t lsm_b = sizeof(float) * v.ncw;
+    const size_t zy_b = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
     const size_t gsm_b = sizeof(float) * (size_t)std::max(0, rg - 1) * F;
     const size_t gout_b = v.xb ? 8 * (size_t)a.Fp : 0;
     const size_t gin_b = v.xb ? 8 * (size_t)a.Fp * a.krep : 0;
     const size_t wsm_b = v.ws ? sizeof(float) * (size_t)F : 0;
-    const size_t fixed = red_b + lsm_b + gsm_b + gout_b + gin_b + wsm_b + 512;
+    const size_t fixed = red_b + zy_b + gsm_b + gout_b + gin_b + wsm_b + 512;
     const size_t slot_b = (size_t)v.rs * a.row_bytes;
     if (slot_b > (1u << 20) - 16 || h->smem_optin < fixed + 16 + slot_b) {
         *why = "a ring slot does not fit in shared memory";
@@ -292,7 +299,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     size_t off = (size_t)a.ns * slot_b;
     off = align_up(off, 16); a.off_bar = (int)off;   off += 8 * (2 * ns + 2);
     off = align_up(off, 16); a.off_red = (int)off;   off += red_b;
-    a.off_lsm = (int)off;                            off += lsm_b;
+    off = align_up(off, 16); a.off_zy = (int)off;    off += zy_b;
     off = align_up(off, 16); a.off_gsm = (int)off;   off += gsm_b;
     off = align_up(off, 128); a.off_gout = (int)off; off += gout_b;
     off = align_up(off, 128); a.off_gin = (int)off;  off += gin_b;
@@ -344,6 +351,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
     }
     int done = 0;
     *h->h_err = 0;
+    if (want_loss) CK(h, cudaMemsetAsync(h->loss_fix, 0, 8 * (size_t)n_steps, h->stream));
     while (done < n_steps) {
         const int n = std::min(max_per_launch, n_steps - done);
         // 32-bit flag wrap: equality compare makes wrap harmless, but never emit flag 0
@@ -358,7 +366,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         a.acc = h->acc;
         a.counter = h->counter;
         a.wmaster = h->wmaster;
-        a.loss_out = want_loss ? h->d_loss + done : nullptr;
+        a.loss_fix = want_loss ? h->loss_fix + done : nullptr;
         // accumulators and the arrival counter start every launch at zero
         CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 4, h->stream));
@@ -384,6 +392,12 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         h->launches++;
         h->step += n;
         done += n;
+    }
+    if (want_loss) {
+        slk::loss_finish_kernel<<<(n_steps + 255) / 256, 256, 0, h->stream>>>(
+            h->loss_fix, h->d_loss, n_steps, 1.0 / (double)h->B);
+        h->launches++;
+        CK(h, cudaGetLastError());
     }
     h->path_used = 1;
     h->variant_used = plan.variant + 1;
@@ -547,7 +561,7 @@ int sl_destroy(sl_handle* h) {
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->model); cudaFree(h->old); cudaFree(h->shard);
-    cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->d_loss);
+    cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->d_loss); cudaFree(h->loss_fix);
     cudaFree(h->dbg);
     cudaFree(h->resid); cudaFree(h->rowloss); cudaFree(h->gpart); cudaFree(h->gsum);
     if (h->h_in) cudaFreeHost(h->h_in);
@@ -580,6 +594,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "step") h->step = value;
     else if (k == "debug_timeline") h->opt_dbg_step = value;
     else if (k == "ring_slots") h->opt_ring = value;
+    else if (k == "krep") h->opt_krep = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
 }

@@ -17,6 +17,8 @@ ap.add_argument("--variants", default="1,2,3")
 ap.add_argument("--grids", default="0")
 ap.add_argument("--paths", default="1")
 ap.add_argument("--ring", type=int, default=0)
+ap.add_argument("--krep", type=int, default=0)
+ap.add_argument("--loss", type=int, default=0)
 a = ap.parse_args()
 peak = 6538.3
 algo = 4 * (a.F + 1) * a.B + 16 * a.F
@@ -25,12 +27,12 @@ with Replica(a.F, a.B) as r:
     for path in [int(x) for x in a.paths.split(",")]:
         for v in [int(x) for x in a.variants.split(",")]:
             for g in [int(x) for x in a.grids.split(",")]:
-                r.set_option("ring_slots", a.ring); r.set_option("path", path); r.set_option("variant", v); r.set_option("grid", g)
+                r.set_option("ring_slots", a.ring); r.set_option("krep", a.krep); r.set_option("path", path); r.set_option("variant", v); r.set_option("grid", g)
                 try:
                     r.train_steps(64, want_loss=False)
                     best = 1e9
                     for _ in range(3):
-                        r.train_steps(a.steps, want_loss=False)
+                        r.train_steps(a.steps, want_loss=bool(a.loss))
                         best = min(best, r.last_train_ms())
                     us = best * 1e3 / a.steps
                     print(f"path={path} variant={v} grid={r.info('grid')} slots={r.info('ring_slots')} "

@@ -22,8 +22,8 @@ with Replica(F, B) as r:
     rc = r._L.sl_debug_read(r._h, buf.ctypes.data_as(C.POINTER(C.c_ulonglong)), buf.size)
     assert rc == 0
     t = buf.reshape(4, G, 8, 2).astype(np.int64)
-names = ["P0 step start", "P1 compute done", "P2 partial stored", "P3 owner done", "P4 w received", "P5 first rows in regs"]
-order = [0, 5, 1, 2, 3, 4]
+names = ["P0 step start", "P1 compute done", "P2 gradient staged", "P3 counter bumped", "P4 total load issued", "P5 weights applied", "P6 exch saw gradient", "P7 reduce wait_group done"]
+order = [0, 5, 1, 2, 6, 7, 3, 4]
 for s in range(1, 3):
     g0 = t[s, :, 0, 1].min()
     print(f"--- step {100 + s}: globaltimer ns relative to earliest CTA step start (min / median / max over CTAs)")
