@@ -134,6 +134,32 @@ int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128);
 int sl_allreduce_avg(sl_handle* h);
 int sl_train_steps_sync(sl_handle* h, int n_steps, double* loss_out);
 
+/* ---- allocation-free step ------------------------------------------------------------
+ * No counterpart in the reference (which never touches a GPU): one minibatch step
+ * (step index t, rows (t*B + j) mod n_rows, same three kernels as sl_train_steps' simple
+ * path) for callers that must not allocate device memory.  Two kinds of caller in this
+ * system are in that position: a worker that shares its B200 with other worker replicas
+ * (BASELINE config 2 runs four on one GPU) — cudaMalloc/cudaFree synchronise the whole
+ * device and would stall the neighbours' streams — and a worker whose resident shard was
+ * sized to fill HBM, for which any further allocation fails.  So this entry point takes no
+ * handle and calls no cudaMalloc/cudaFree or other allocating routine: its scratch is a
+ * fixed array inside the library image (about 2.06 MiB per GPU that loads the library, held
+ * until the process exits).
+ *   - d_X [n_rows*F] fp32, d_y [n_rows] fp32, d_model [F] fp64 (updated in place) and
+ *     d_loss (nullable, 1 fp64) are DEVICE pointers on `device`, owned by the caller.
+ *   - limits: B <= 8192, F <= 4096; larger shapes return SL_EINVAL (see sl_last_error(NULL)).
+ *   - asynchronous: the three kernels are enqueued on `stream` (a cudaStream_t, NULL = the
+ *     default stream); results are ready when the stream reaches that point.
+ *   - the first call on a device looks up the scratch's device address
+ *     (cudaGetSymbolAddress); make that first call before starting any stream capture.
+ *   - every call on a device uses the same scratch, which keeps whatever the last call left
+ *     there (nothing in it needs clearing: each call overwrites all it reads).  Two calls
+ *     whose kernels overlap on the GPU — different streams, or two threads — race on it;
+ *     serialise them. */
+int sl_lr_step_noalloc(int device, const float* d_X, const float* d_y, long long n_rows, int F,
+                       int B, long long t, double eta, double* d_model, double* d_loss,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif

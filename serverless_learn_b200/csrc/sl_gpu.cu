@@ -916,3 +916,91 @@ int sl_allreduce_avg(sl_handle* h) {
 }
 
 }  // extern "C"
+
+// =====================================================================================
+// Allocation-free minibatch step
+// =====================================================================================
+// Scratch of sl_lr_step_noalloc: residuals, per-row losses and the row-split gradient
+// partials of ONE step.  It lives in the module image, so every GPU that loads this
+// library carries these bytes until the process exits; every call on a device shares it.
+#define SL_NOALLOC_MAX_B 8192
+#define SL_NOALLOC_MAX_F 4096
+#define SL_NOALLOC_GPART_FLOATS (512 * 1024)
+#define SL_NOALLOC_SCRATCH_BYTES \
+    (sizeof(float) * (2 * SL_NOALLOC_MAX_B + SL_NOALLOC_GPART_FLOATS))
+static __device__ __align__(256) unsigned char sl_noalloc_scratch[SL_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kNaMaxDevices = 64;
+std::mutex g_na_mu;
+unsigned char* g_na_ptr[kNaMaxDevices] = {nullptr};  // device address of the scratch, per device
+int g_na_sms[kNaMaxDevices] = {0};
+}  // namespace
+
+extern "C" int sl_lr_step_noalloc(int device, const float* d_X, const float* d_y, long long n_rows,
+                                  int F, int B, long long t, double eta, double* d_model,
+                                  double* d_loss, void* stream) {
+    if (!d_X || !d_y || !d_model) return fail(nullptr, SL_EINVAL, "sl_lr_step_noalloc: NULL buffer");
+    if (n_rows <= 0 || F <= 0 || B <= 0 || t < 0)
+        return fail(nullptr, SL_EINVAL, "sl_lr_step_noalloc: n_rows, F, B must be positive, t >= 0");
+    if (B > SL_NOALLOC_MAX_B || F > SL_NOALLOC_MAX_F)
+        return fail(nullptr, SL_EINVAL,
+                    "sl_lr_step_noalloc: B = %d / F = %d exceed the built-in scratch "
+                    "(B <= %d, F <= %d); use sl_train_steps for larger shapes",
+                    B, F, SL_NOALLOC_MAX_B, SL_NOALLOC_MAX_F);
+    if (device < 0 || device >= kNaMaxDevices)
+        return fail(nullptr, SL_EINVAL, "sl_lr_step_noalloc: device %d out of range", device);
+    DeviceGuard dg(device);
+    unsigned char* base = nullptr;
+    int sms = 0;
+    {
+        // One-time set-up per device, with that device current.  The array's name is only
+        // a host-side handle; the address a kernel can use comes from the runtime.
+        std::lock_guard<std::mutex> lk(g_na_mu);
+        if (!g_na_ptr[device]) {
+            void* p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&p, sl_noalloc_scratch);
+            if (e != cudaSuccess || !p) {
+                cudaGetLastError();
+                return fail(nullptr, SL_ECUDA, "cudaGetSymbolAddress(sl_noalloc_scratch) failed: %s",
+                            cudaGetErrorString(e));
+            }
+            int v = 0;
+            e = cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device);
+            if (e != cudaSuccess || v <= 0) {
+                cudaGetLastError();
+                return fail(nullptr, SL_ECUDA, "cudaDeviceGetAttribute failed: %s",
+                            cudaGetErrorString(e));
+            }
+            g_na_sms[device] = v;
+            g_na_ptr[device] = static_cast<unsigned char*>(p);
+        }
+        base = g_na_ptr[device];
+        sms = g_na_sms[device];
+    }
+    float* resid = reinterpret_cast<float*>(base);
+    float* rowloss = resid + SL_NOALLOC_MAX_B;
+    float* gpart = rowloss + SL_NOALLOC_MAX_B;
+    // same row split as sl_train_steps' simple path, capped by the scratch
+    const int col_blocks = (F + 127) / 128;
+    int want = std::max(1, (4 * sms + col_blocks - 1) / col_blocks);
+    want = std::min(want, B);
+    want = std::min<long long>(want, SL_NOALLOC_GPART_FLOATS / F);
+    const int rows_per_split = (B + want - 1) / want;
+    const int nsplit = (B + rows_per_split - 1) / rows_per_split;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long mb = (long long)(((__int128)t * B) % n_rows);
+    const int wpb = 8;
+    // nothing in the scratch has to start at zero: the three kernels overwrite every word
+    // they later read
+    slk::lr_fwd_kernel<<<(B + wpb - 1) / wpb, wpb * 32, 0, st>>>(d_X, d_y, n_rows, F, B, mb, d_model,
+                                                               resid, rowloss);
+    slk::lr_grad_kernel<<<dim3(col_blocks, nsplit), 128, 0, st>>>(d_X, n_rows, F, B, mb, resid, gpart,
+                                                                  rows_per_split);
+    slk::lr_finish_kernel<<<(F + 255) / 256, 256, 0, st>>>(gpart, nsplit, F, B, rowloss, d_model,
+                                                           eta / (double)B, d_loss, nullptr, 0);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess)
+        return fail(nullptr, SL_ECUDA, "sl_lr_step_noalloc: launch failed: %s", cudaGetErrorString(e));
+    return SL_OK;
+}
