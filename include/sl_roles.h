@@ -1,0 +1,94 @@
+/*
+ * sl_roles.h — C ABI over the host-side role cores (WorkerCore, MasterCore, FileServerCore):
+ * the reference's three programs with the gRPC types replaced by plain buffers, on top of
+ * the GPU ABI of sl_gpu.h.  Each entry cites the handler / loop it mirrors (file:line in the
+ * reference).  "addr" strings play the part of the reference's "host:port" addresses; an
+ * in-process directory (slr_directory_*) stands in for grpc::CreateChannel(addr).
+ * Return convention: handlers that answer with an `ok` bool in the reference return 1/0.
+ */
+#ifndef SL_ROLES_H
+#define SL_ROLES_H
+
+#include <stddef.h>
+
+#include "sl_gpu.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct slr_worker slr_worker;
+typedef struct slr_master slr_master;
+typedef struct slr_file_server slr_file_server;
+typedef struct slr_directory slr_directory;
+
+/* ---- Update wire format (src/protos/serverless_learn.proto:81-83, proto3 packed) ------- */
+long slr_update_encode(const double* delta, int n, void* out, long cap); /* bytes, -1 = cap */
+int slr_update_decode(const void* buf, long len, double* out, int cap);  /* count, -1 = bad */
+
+/* ---- directory: addr -> worker (stand-in for CreateChannel, src/worker.cc:210) ---------- */
+int slr_directory_create(slr_directory** out);
+void slr_directory_destroy(slr_directory* d);
+int slr_directory_add(slr_directory* d, const char* addr, slr_worker* w);
+
+/* ---- file server (src/file_server.cc) ---------------------------------------------------- */
+/* builds file 0 exactly as main() does (:152-156): 100,000,000 bytes of
+ * independent_bits_engine<default_random_engine, 8, unsigned char>, restated */
+int slr_file_server_create(slr_file_server** out);
+void slr_file_server_destroy(slr_file_server* fs);
+long long slr_file_server_file_length(slr_file_server* fs);
+/* chunk k of the stream WorkerStub::ReceiveFile writes (:60-87); returns its length (0 past
+ * the end) and a pointer valid for the file server's lifetime */
+long long slr_file_server_chunk(slr_file_server* fs, long long k, const void** data);
+/* FileServerImpl::DoPush (:103-119): stream the file to the recipient.  Returns the
+ * PushOutcome ok flag; file_num != 0 returns -1 (the reference calls exit(1), :107-110) */
+int slr_file_server_do_push(slr_file_server* fs, slr_directory* d, const char* recipient_addr,
+                            unsigned file_num);
+int slr_file_server_check_up(slr_file_server* fs); /* :122-130, no-op, returns 1 */
+
+/* ---- master (src/master.cc) ------------------------------------------------------------- */
+int slr_master_create(int device, int D, int B, double eta, double lambda, slr_master** out);
+void slr_master_destroy(slr_master* m);
+sl_handle* slr_master_handle(slr_master* m);
+int slr_master_register_birth(slr_master* m, const char* addr);       /* :79-91 */
+int slr_master_worker_count(slr_master* m);
+const char* slr_master_worker_addr(slr_master* m, int i);
+int slr_master_exchange_updates(slr_master* m, const double* delta, int n, double* reply,
+                                int n_out);                            /* :95-114 */
+/* the same handler fed with serialized Update messages (what a gRPC shim would see) */
+int slr_master_exchange_updates_wire(slr_master* m, const void* in, long in_len, void* out,
+                                     long out_cap, long* out_len);
+/* one round of periodically_request_pushes (:220-237): file 0 to every registered worker, in
+ * registration order; returns the number of successful pushes */
+int slr_master_request_pushes(slr_master* m, slr_file_server* fs, slr_directory* d);
+/* one round of periodically_do_checkups (:240-266): every worker receives the full peer list */
+int slr_master_do_checkups(slr_master* m, slr_file_server* fs, slr_directory* d);
+
+/* ---- worker (src/worker.cc) --------------------------------------------------------------- */
+int slr_worker_create(int device, const char* addr, int D, int F, int B, double eta, double lambda,
+                      slr_worker** out);
+void slr_worker_destroy(slr_worker* w);
+sl_handle* slr_worker_handle(slr_worker* w);
+const char* slr_worker_addr(slr_worker* w);
+/* ReceiveFile (:49-61) as begin / one call per Chunk / end; end returns the ack's ok */
+int slr_worker_receive_begin(slr_worker* w);
+int slr_worker_receive_chunk(slr_worker* w, const void* data, size_t n);
+int slr_worker_receive_end(slr_worker* w);
+int slr_worker_check_up(slr_worker* w, const char* const* peer_addrs, int n); /* :64-77 */
+int slr_worker_peer_count(slr_worker* w);
+const char* slr_worker_peer_addr(slr_worker* w, int i);
+int slr_worker_exchange_updates(slr_worker* w, const double* delta, int n, double* reply,
+                                int n_out);                                    /* :81-100 */
+/* one iteration of periodically_gossip (:194-219) without the sleep: partner = rand() % N over
+ * the peer list; returns the partner index, -1 when there is no peer or the partner cannot be
+ * reached (repair R7: the round is skipped), -2 on a GPU error */
+int slr_worker_gossip_once(slr_worker* w, slr_directory* d);
+/* one iteration of simulate_training (:221-231) without the sleep: the reference's +1 ... */
+int slr_worker_train_tick(slr_worker* w);
+/* ... and what takes its slot in this build */
+int slr_worker_train_steps(slr_worker* w, int n_steps, double* loss_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SL_ROLES_H */

@@ -1,0 +1,106 @@
+// roles.h — host-side role cores: the reference's three programs minus gRPC, over the C ABI
+// of sl_gpu.h.  Same names, argument meaning and error behaviour as the reference's handlers
+// and loops (file:line cited per member), so a gRPC shim is one line per handler.
+#pragma once
+#include <stdint.h>
+
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/sl_gpu.h"
+
+namespace slr {
+
+class WorkerCore;
+
+// addr -> worker; stands in for grpc::CreateChannel(addr) (src/worker.cc:210,
+// src/master.cc:258,284, src/file_server.cc:111-113)
+class Directory {
+  public:
+    void add(const std::string& addr, WorkerCore* w) {
+        std::lock_guard<std::mutex> lk(mu_);
+        map_[addr] = w;
+    }
+    WorkerCore* find(const std::string& addr) {
+        std::lock_guard<std::mutex> lk(mu_);
+        auto it = map_.find(addr);
+        return it == map_.end() ? nullptr : it->second;
+    }
+
+  private:
+    std::mutex mu_;
+    std::map<std::string, WorkerCore*> map_;
+};
+
+// src/worker.cc
+class WorkerCore {
+  public:
+    WorkerCore(int device, const std::string& addr, int D, int F, int B, double eta, double lambda);
+    ~WorkerCore();
+    bool ok() const { return h_ != nullptr; }
+    sl_handle* handle() { return h_; }
+    const std::string& addr() const { return addr_; }
+
+    // WorkerImpl::ReceiveFile, src/worker.cc:49-61 — split at the reader->Read loop
+    bool ReceiveFileBegin();
+    bool ReceiveFileChunk(const void* data, size_t n);
+    bool ReceiveFileEnd();  // ack->ok
+    // WorkerImpl::CheckUp, src/worker.cc:64-77: replace the peer list
+    void CheckUp(const std::vector<std::string>& peer_addrs);
+    std::vector<std::string> peers();
+    // WorkerImpl::ExchangeUpdates, src/worker.cc:81-100
+    bool ExchangeUpdates(const double* delta, int n, double* reply, int n_out);
+    // one iteration of periodically_gossip, src/worker.cc:194-219 (no sleep)
+    int GossipOnce(Directory& dir);
+    // one iteration of simulate_training, src/worker.cc:221-231 (no sleep)
+    bool TrainTick();
+    bool TrainSteps(int n_steps, double* loss_out);
+
+  private:
+    sl_handle* h_ = nullptr;
+    std::string addr_;
+    int D_;
+    std::vector<std::string> peer_list_;  // src/worker.cc:35
+    std::mutex peer_list_mutex_;          // src/worker.cc:37
+};
+
+// src/file_server.cc
+class FileServerCore {
+  public:
+    static constexpr long long kDummyFileLength = 100LL * 1000 * 1000;  // :40
+    static constexpr long long kChunkSize = 1LL * 1000 * 1000;          // :46
+    FileServerCore();  // fills file 0, :152-156
+    const std::string& file() const { return file_; }
+    long long chunk(long long k, const void** data) const;  // :68-76
+    // FileServerImpl::DoPush :103-119 -> WorkerStub::ReceiveFile :60-87.  -1: file_num != 0
+    int DoPush(Directory& dir, const std::string& recipient_addr, uint32_t file_num);
+    bool CheckUp() const { return true; }  // :122-130
+
+  private:
+    std::string file_;  // :43
+};
+
+// src/master.cc
+class MasterCore {
+  public:
+    MasterCore(int device, int D, int B, double eta, double lambda);
+    ~MasterCore();
+    bool ok() const { return h_ != nullptr; }
+    sl_handle* handle() { return h_; }
+    bool RegisterBirth(const std::string& addr);  // :79-91, append-only, no de-duplication
+    std::vector<std::string> workers();
+    bool ExchangeUpdates(const double* delta, int n, double* reply, int n_out);  // :95-114
+    int RequestPushes(FileServerCore& fs, Directory& dir);  // one round of :220-237
+    int DoCheckups(FileServerCore& fs, Directory& dir);     // one round of :240-266
+
+  private:
+    sl_handle* h_ = nullptr;
+    int D_;
+    std::vector<std::string> workers_;  // :63 (WorkerInfo holds only the address, :49-56)
+    std::mutex workers_mutex_;          // :66
+};
+
+}  // namespace slr

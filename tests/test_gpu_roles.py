@@ -1,0 +1,101 @@
+"""GPU: the role cores (WorkerCore / MasterCore / FileServerCore, include/sl_roles.h) run a
+whole in-process job — registration, check-ups, file push, training ticks, gossip, exchange
+with the master — and every replica is compared with an oracle simulation of the same
+deterministic schedule (repair R8: one schedule instead of racing threads)."""
+import ctypes as C
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_reference_job_in_process(orc, file0):
+    from serverless_learn_b200 import roles
+    F, B, NW = 1024, 4096, 3
+    d, fs = roles.Directory(), roles.FileServer()
+    master = roles.Master(F)
+    ws = [roles.Worker(f"localhost:{50060 + k}", F, B) for k in range(NW)]
+    for w in ws:
+        d.add(w)
+        assert master.register_birth(w.addr)           # src/worker.cc:249-252
+    assert master.workers() == [w.addr for w in ws]    # registration order, append-only
+    assert master.do_checkups(fs, d) == NW             # src/master.cc:240-266
+    for w in ws:
+        assert w.peers() == [x.addr for x in ws]       # full list, self included
+    # push: every registered worker gets file 0 (src/master.cc:231-235)
+    assert master.request_pushes(fs, d) == NW
+    L = roles._lib.load()
+    for w in ws:
+        s, wsum = C.c_ulonglong(), C.c_ulonglong()
+        assert L.sl_shard_checksum(w.handle, C.byref(s), C.byref(wsum)) == 0
+        assert s.value == 12_749_417_848 and wsum.value == orc.weighted_sum(file0[0])
+    # oracle replicas
+    om = [np.zeros(F) for _ in range(NW)]
+    oo = [np.zeros(F) for _ in range(NW)]
+    mm, mo = np.zeros(F), np.zeros(F)
+    # the gossip partner is rand() % N of THIS process: replay the same glibc stream
+    libc = C.CDLL("libc.so.6")
+    libc.srand(12345)
+    draws = [libc.rand() for _ in range(6)]
+    libc.srand(12345)
+    it = iter(draws)
+    for rnd in range(2):
+        for k, w in enumerate(ws):
+            for _ in range(k + 1):                     # simulate_training ticks, src/worker.cc:225-227
+                assert w.train_tick()
+                orc.train_tick(om[k])
+        for k, w in enumerate(ws):                     # periodically_gossip, src/worker.cc:194-219
+            j = w.gossip_once(d)
+            assert j == next(it) % NW
+            delta = orc.delta(om[k], oo[k])
+            if j == k:                                 # a worker may draw itself (list includes it)
+                reply = orc.merge_callee(om[k], oo[k], delta)
+            else:
+                reply = orc.merge_callee(om[j], oo[j], delta)
+            orc.apply_reply(om[k], oo[k], reply)
+        # R9: a worker also exchanges with the master (Master::ExchangeUpdates, proto:13)
+        delta = orc.delta(om[0], oo[0])
+        reply = master.exchange_updates(delta)
+        assert np.array_equal(reply, orc.merge_callee(mm, mo, delta))
+    for k, w in enumerate(ws):
+        assert np.array_equal(w.model(), om[k]), k
+    assert np.array_equal(master.model(), mm)
+    # wire-level handler == plain handler
+    raw = orc.update_encode(np.arange(F, dtype=np.float64))
+    back = orc.update_decode(master.exchange_updates_wire(raw))
+    assert np.array_equal(back, orc.merge_callee(mm, mo, np.arange(F, dtype=np.float64)))
+    for w in ws:
+        w.close()
+    master.close()
+    fs.close()
+    d.close()
+
+
+def test_gossip_without_peers_skips_the_round():
+    from serverless_learn_b200 import roles
+    d = roles.Directory()
+    w = roles.Worker("a:1", 8, 4)
+    assert w.gossip_once(d) == -1                      # R7 (reference: rand() % 0)
+    w.check_up(["ghost:9"])
+    assert w.gossip_once(d) == -1                      # unreachable partner
+    w.close()
+    d.close()
+
+
+def test_worker_trains_on_pushed_synthetic_shard(orc):
+    from serverless_learn_b200 import roles
+    F, B, n = 64, 32, 500
+    X, y = orc.synth(0, n, F)
+    w = roles.Worker("a:1", F, B, eta=0.3)
+    stream = np.concatenate([X.reshape(-1), y]).view(np.uint8)
+    chunks = [stream[i:i + 1000] for i in range(0, stream.size, 1000)]   # rows straddle chunks
+    assert w.receive_file(chunks)
+    lg = w.train_steps(10)
+    ref = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, 10, ref, 0.3)
+    assert np.max(np.abs(w.model() - ref)) / np.max(np.abs(ref)) <= 1e-5
+    assert np.max(np.abs(lg - lo) / lo) <= 1e-5
+    w.close()
