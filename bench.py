@@ -40,6 +40,11 @@ METRIC = "training samples/sec"
 UNIT = "samples/s"
 
 
+def shard_row0(rank: int, rows_per_gpu: int = ROWS_PER_GPU) -> int:
+    """Worker k <-> GPU k owns rows [k*rows_per_gpu, (k+1)*rows_per_gpu) of the synthetic matrix."""
+    return rank * rows_per_gpu
+
+
 def algorithmic_bytes_per_step(f=F, b=B) -> int:
     # SURVEY.md §8(d): 4*(F+1) per sample (row + label) + 16*F per step (fp64 w read+write)
     return 4 * (f + 1) * b + 16 * f
@@ -196,7 +201,7 @@ def run_b200(args, rank, world, local_rank):
         return float(t.item())
 
     r = Replica(F, B, eta=ETA, device=local_rank)
-    r.shard_synth(ROWS_PER_GPU, row0=rank * ROWS_PER_GPU)
+    r.shard_synth(ROWS_PER_GPU, row0=shard_row0(rank))
     if multi:
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
@@ -206,13 +211,13 @@ def run_b200(args, rank, world, local_rank):
     step_fn = r.train_steps_sync if multi else r.train_steps
 
     # ---- device-resident leg ("value") ------------------------------------------------
-    step_fn(args.warmup, want_loss=False)
+    step_fn(args.warmup, want_loss=True)
     sampler = ClockSampler(local_rank)
     barrier()
     l0 = r.info("launches")
     sampler.start()
     t0 = time.perf_counter()
-    step_fn(args.steps, want_loss=False)
+    step_fn(args.steps, want_loss=True)      # every step's loss is computed and read back
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
     sampler.stop_flag = True
@@ -231,7 +236,7 @@ def run_b200(args, rank, world, local_rank):
     # own generator and read back once, outside any timed region
     gen = Replica(F, B, eta=ETA, device=local_rank)
     for i, hb in enumerate(host):
-        gen.shard_synth(B, row0=rank * ROWS_PER_GPU + i * B)
+        gen.shard_synth(B, row0=shard_row0(rank) + i * B)
         raw = gen.shard_read(0, gen.shard_bytes())
         hb.copy_(torch.from_numpy(raw.view(np.float32)))
     gen.close()
