@@ -73,7 +73,10 @@ int sl_debug_read(sl_handle* h, unsigned long long* out, size_t n_words);
  * each Chunk and drops it.  Call sl_shard_begin once per stream, sl_shard_append
  * once per Chunk (any length, any alignment; rows may straddle calls) and
  * sl_shard_end when reader->Read returns false.  Bytes go through a pinned ring to
- * a resident HBM buffer; a pinned source is DMA'd directly.  The byte stream is
+ * a resident HBM buffer; a page-locked source is DMA'd directly and asynchronously, and —
+ * the one exception to "buffers are used only during the call" — must stay valid until
+ * sl_shard_end returns.  The previously sealed shard stays trainable until sl_shard_end
+ * swaps the new one in, so ingest overlaps training.  The byte stream is
  * kept verbatim: n_rows = floor(len / (4*(F+1))); the first n_rows*F fp32 are X
  * (row-major), the next n_rows fp32 are the labels.  size_hint = expected length
  * in bytes (0 = unknown, the buffer then grows by doubling). */

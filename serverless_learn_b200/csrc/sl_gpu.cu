@@ -112,6 +112,9 @@ struct sl_handle {
     // shard
     unsigned char* shard = nullptr;
     size_t shard_cap = 0, shard_len = 0;
+    // incoming stream (sl_shard_begin .. sl_shard_end) lands here while `shard` stays trainable
+    unsigned char* in_buf = nullptr;
+    size_t in_cap = 0, in_len = 0;
     long long n_rows = 0;
     bool shard_open = false, shard_sealed = false;
     unsigned char* stage[kStageSlots] = {nullptr, nullptr, nullptr, nullptr};
@@ -183,9 +186,11 @@ struct DeviceGuard {
     }
 };
 
-int ensure_shard_cap(sl_handle* h, size_t need) {
-    if (need <= h->shard_cap) return SL_OK;
-    size_t cap = std::max(need, std::max(h->shard_cap * 2, kDefaultShardCap));
+int ensure_buf_cap(sl_handle* h, unsigned char** buf, size_t* cap_io, size_t len, size_t need,
+                   bool exact = false) {
+    if (need <= *cap_io) return SL_OK;
+    size_t cap = std::max(need, std::max(*cap_io * 2, kDefaultShardCap));
+    if (exact) cap = std::max<size_t>(need, 1u << 20);  // caller told us the size
     unsigned char* nb = nullptr;
     cudaError_t e = cudaMalloc(&nb, cap);
     if (e != cudaSuccess) {
@@ -193,13 +198,13 @@ int ensure_shard_cap(sl_handle* h, size_t need) {
         return fail(h, SL_ENOMEM, "cudaMalloc(%zu) for the shard failed: %s", cap,
                     cudaGetErrorString(e));
     }
-    if (h->shard && h->shard_len) {
-        CK(h, cudaMemcpyAsync(nb, h->shard, h->shard_len, cudaMemcpyDeviceToDevice, h->copy_stream));
-        CK(h, cudaStreamSynchronize(h->copy_stream));
+    if (*buf && len) {
+        CK(h, cudaMemcpyAsync(nb, *buf, len, cudaMemcpyDeviceToDevice, h->copy_stream));
     }
-    if (h->shard) cudaFree(h->shard);
-    h->shard = nb;
-    h->shard_cap = cap;
+    CK(h, cudaStreamSynchronize(h->copy_stream));  // also drains DMAs still aimed at the old buffer
+    if (*buf) cudaFree(*buf);
+    *buf = nb;
+    *cap_io = cap;
     return SL_OK;
 }
 
@@ -560,7 +565,7 @@ int sl_destroy(sl_handle* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    cudaFree(h->model); cudaFree(h->old); cudaFree(h->shard);
+    cudaFree(h->model); cudaFree(h->old); cudaFree(h->shard); cudaFree(h->in_buf);
     cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->d_loss); cudaFree(h->loss_fix);
     cudaFree(h->dbg);
     cudaFree(h->resid); cudaFree(h->rowloss); cudaFree(h->gpart); cudaFree(h->gsum);
@@ -622,13 +627,14 @@ int sl_shard_begin(sl_handle* h, size_t size_hint) {
     if (!h) return SL_EINVAL;
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard dg(h->device);
-    CK(h, cudaStreamSynchronize(h->stream));  // no kernel may still read the old shard
-    h->shard_len = 0;
-    h->n_rows = 0;
-    h->shard_sealed = false;
+    // The sealed shard stays valid and trainable; the stream lands in a second buffer that
+    // sl_shard_end swaps in (the reference receives files on a gRPC thread while the training
+    // thread keeps running, src/worker.cc:242-246).
+    CK(h, cudaStreamSynchronize(h->copy_stream));
+    h->in_len = 0;
     h->shard_open = true;
     if (size_hint) {
-        int rc = ensure_shard_cap(h, size_hint);
+        int rc = ensure_buf_cap(h, &h->in_buf, &h->in_cap, 0, size_hint, true);
         if (rc) return rc;
     }
     return SL_OK;
@@ -641,17 +647,18 @@ int sl_shard_append(sl_handle* h, const void* bytes, size_t n) {
     if (n == 0) return SL_OK;
     if (!bytes) return fail(h, SL_EINVAL, "bytes is NULL");
     DeviceGuard dg(h->device);
-    int rc = ensure_shard_cap(h, h->shard_len + n);
+    int rc = ensure_buf_cap(h, &h->in_buf, &h->in_cap, h->in_len, h->in_len + n);
     if (rc) return rc;
     cudaPointerAttributes at;
     bool pinned = false;
     if (cudaPointerGetAttributes(&at, bytes) == cudaSuccess) pinned = at.type == cudaMemoryTypeHost;
     else cudaGetLastError();
     if (pinned) {
-        // the caller's buffer is page-locked: DMA straight from it
-        CK(h, cudaMemcpyAsync(h->shard + h->shard_len, bytes, n, cudaMemcpyHostToDevice,
+        // The caller's buffer is page-locked: DMA straight from it, asynchronously.  This is the
+        // one exception to "buffers are used only for the duration of the call": a page-locked
+        // source must stay valid until sl_shard_end returns (it waits for the copies).
+        CK(h, cudaMemcpyAsync(h->in_buf + h->in_len, bytes, n, cudaMemcpyHostToDevice,
                               h->copy_stream));
-        CK(h, cudaStreamSynchronize(h->copy_stream));  // caller owns the buffer only for the call
     } else {
         const unsigned char* src = static_cast<const unsigned char*>(bytes);
         size_t off = 0;
@@ -660,14 +667,14 @@ int sl_shard_append(sl_handle* h, const void* bytes, size_t n) {
             const int s = h->stage_idx;
             CK(h, cudaEventSynchronize(h->stage_ev[s]));  // slot's previous DMA done
             memcpy(h->stage[s], src + off, m);
-            CK(h, cudaMemcpyAsync(h->shard + h->shard_len + off, h->stage[s], m,
+            CK(h, cudaMemcpyAsync(h->in_buf + h->in_len + off, h->stage[s], m,
                                   cudaMemcpyHostToDevice, h->copy_stream));
             CK(h, cudaEventRecord(h->stage_ev[s], h->copy_stream));
             h->stage_idx = (s + 1) % kStageSlots;
             off += m;
         }
     }
-    h->shard_len += n;
+    h->in_len += n;
     return SL_OK;
 }
 
@@ -677,6 +684,11 @@ int sl_shard_end(sl_handle* h, long long* n_rows) {
     if (!h->shard_open) return fail(h, SL_ESTATE, "sl_shard_end without sl_shard_begin");
     DeviceGuard dg(h->device);
     CK(h, cudaStreamSynchronize(h->copy_stream));
+    CK(h, cudaStreamSynchronize(h->stream));  // no kernel may still read the outgoing shard
+    std::swap(h->shard, h->in_buf);
+    std::swap(h->shard_cap, h->in_cap);
+    h->shard_len = h->in_len;
+    h->in_len = 0;
     h->shard_open = false;
     h->shard_sealed = true;
     h->n_rows = (long long)(h->shard_len / (4 * ((size_t)h->F + 1)));
@@ -735,7 +747,7 @@ int sl_shard_synth(sl_handle* h, long long n_rows, unsigned long long row0,
     CK(h, cudaStreamSynchronize(h->stream));
     const size_t bytes = (size_t)n_rows * 4 * ((size_t)h->F + 1);
     h->shard_len = 0;
-    int rc = ensure_shard_cap(h, bytes);
+    int rc = ensure_buf_cap(h, &h->shard, &h->shard_cap, 0, bytes, true);
     if (rc) return rc;
     float* X = reinterpret_cast<float*>(h->shard);
     float* y = X + (size_t)n_rows * h->F;
