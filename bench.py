@@ -172,7 +172,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------
@@ -200,6 +200,14 @@ def run_b200(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def attach_peers(rep):
+        """Exchange the 64-byte IPC handles of the replicas' inboxes: the fused kernel then sums
+        gradients across GPUs through peer memory (NVLink), no per-step collective launch."""
+        mine = torch.frombuffer(bytearray(rep.peer_export()), dtype=torch.uint8).cuda()
+        allh = [torch.zeros(64, dtype=torch.uint8, device="cuda") for _ in range(world)]
+        dist.all_gather(allh, mine)
+        rep.peer_attach(world, rank, b"".join(bytes(t.cpu().numpy().tobytes()) for t in allh))
+
     r = Replica(F, B, eta=ETA, device=local_rank)
     r.shard_synth(ROWS_PER_GPU, row0=shard_row0(rank))
     if multi:
@@ -208,6 +216,7 @@ def run_b200(args, rank, world, local_rank):
             uid.copy_(torch.frombuffer(bytearray(Replica.comm_unique_id()), dtype=torch.uint8))
         dist.broadcast(uid, 0)
         r.comm_init_rank(world, rank, bytes(uid.cpu().numpy().tobytes()))
+        attach_peers(r)
     step_fn = r.train_steps_sync if multi else r.train_steps
 
     # ---- device-resident leg ("value") ------------------------------------------------
@@ -215,6 +224,7 @@ def run_b200(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank)
     barrier()
     l0 = r.info("launches")
+    k0 = r.info("k1_launches")
     sampler.start()
     t0 = time.perf_counter()
     step_fn(args.steps, want_loss=True)      # every step's loss is computed and read back
@@ -223,6 +233,7 @@ def run_b200(args, rank, world, local_rank):
     sampler.stop_flag = True
     dev_ms = r.last_train_ms()
     launches = r.info("launches") - l0
+    k1 = max(1, r.info("k1_launches") - k0) if r.info("path") in (1, 4) else max(1, launches)
     barrier()
     sampler.join(timeout=1.0)
     dev_s = max_over_ranks(dev_ms * 1e-3)
@@ -249,6 +260,7 @@ def run_b200(args, rank, world, local_rank):
             uid2.copy_(torch.frombuffer(bytearray(Replica.comm_unique_id()), dtype=torch.uint8))
         dist.broadcast(uid2, 0)
         e2e.comm_init_rank(world, rank, bytes(uid2.cpu().numpy().tobytes()))
+        attach_peers(e2e)
     e2e_step = e2e.train_steps_sync if multi else e2e.train_steps
 
     def ingest(i):
@@ -300,8 +312,8 @@ def run_b200(args, rank, world, local_rank):
 
     if rank == 0:
         peak, peak_src = measured_peak()
-        algo = algorithmic_bytes_per_step() * args.steps / max(launches, 1)
-        per_launch_s = dev_ms * 1e-3 / max(launches, 1)
+        algo = algorithmic_bytes_per_step() * args.steps / k1
+        per_launch_s = dev_ms * 1e-3 / k1
         achieved = algo / per_launch_s / 1e9
         traffic = ncu_traffic_per_step()
         line = {
@@ -313,17 +325,19 @@ def run_b200(args, rank, world, local_rank):
                                    f": logistic regression F={F}, B={B} per GPU, "
                                    f"{ROWS_PER_GPU} rows x {F} fp32 resident per GPU",
                        "l2": "inputs larger than L2 (4 GiB shard per GPU, sequential minibatches)",
-                       "parallelism": f"dp{world}" + (" (NCCL all-reduce of the gradient every step)" if multi else ""),
-                       "kernel_path": {1: "persistent", 2: "simple", 3: "simple+nccl"}.get(r.info("path"), "?"),
+                       "parallelism": f"dp{world}" + (" (gradient summed across GPUs every step inside the persistent "
+                                                      "kernel, through peer memory over NVLink)" if multi else ""),
+                       "kernel_path": {1: "persistent", 2: "simple", 3: "simple+nccl",
+                                       4: "persistent+peer-memory exchange"}.get(r.info("path"), "?"),
                        "variant": r.info("variant"), "grid": r.info("grid"),
                        "ring_slots": r.info("ring_slots")},
             "wall_ms_per_step": 1e3 * wall_s / args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None if traffic is None else traffic * args.steps / max(launches, 1),
+                         "frac": achieved / peak, "traffic": None if traffic is None else traffic * args.steps / k1,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_step": algorithmic_bytes_per_step(),
-                         "kernel": "lr_persist_kernel" if r.info("path") == 1 else "lr_fwd+lr_grad+lr_finish",
-                         "launches": launches},
+                         "kernel": "lr_persist_kernel" if r.info("path") in (1, 4) else "lr_fwd+lr_grad+lr_finish",
+                         "launches": k1},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                     "d2h_bytes_per_step": 8, "steps": e2e_steps, "last_loss": float(loss)},
             "e2e_resident": {"value": world * res_steps * B / res_s, "unit": UNIT,
@@ -335,14 +349,29 @@ def run_b200(args, rank, world, local_rank):
         }
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_port()
-        print(json.dumps(line), flush=True)
+        emit(line)
     r.close()
     e2e.close()
     if multi:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line goes to the real stdout; everything else any library prints to fd 1
+    (NCCL's version banner, for one) has been routed to stderr."""
+    out = os.fdopen(os.dup(_REAL_STDOUT), "w") if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=4096)

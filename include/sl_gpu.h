@@ -132,6 +132,16 @@ int sl_set_state(sl_handle* h, const double* model, const double* old, int n);
  * call sl_comm_init_rank on every rank.  NCCL is resolved with dlopen at that
  * point.  sl_allreduce_avg: model <- mean over ranks of model (one ncclAllReduce).
  * sl_train_steps_sync: n_steps of { local gradient; all-reduce; update }. */
+/* Fused path (preferred): sl_peer_export yields a 64-byte IPC handle of this replica's inbox;
+ * gather the handles of all ranks (rank order) and pass them to sl_peer_attach on every rank
+ * (1 <= nranks <= 8, one process per GPU, same box).  sl_train_steps_sync then runs ALL steps
+ * in one persistent kernel per GPU: the kernels exchange 32-element slices of the exact integer
+ * gradient sum through peer-mapped memory over NVLink, no host-launched collective per step.
+ * Every rank must call sl_train_steps_sync with the same n_steps at about the same time (the
+ * kernels wait for one another).  With NCCL also initialised the returned losses are the mean
+ * over ranks, otherwise this rank's own.  Option "sync_path" = 1 forces the NCCL path. */
+int sl_peer_export(sl_handle* h, void* handle64);
+int sl_peer_attach(sl_handle* h, int nranks, int rank, const void* handles);
 int sl_comm_unique_id(void* id128);
 int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128);
 int sl_allreduce_avg(sl_handle* h);

@@ -36,6 +36,8 @@ _SIGS = {
     "sl_get_model": (C.c_int, [_h, _dp, C.c_int]),
     "sl_get_old": (C.c_int, [_h, _dp, C.c_int]),
     "sl_set_state": (C.c_int, [_h, _dp, _dp, C.c_int]),
+    "sl_peer_export": (C.c_int, [_h, C.c_void_p]),
+    "sl_peer_attach": (C.c_int, [_h, C.c_int, C.c_int, C.c_void_p]),
     "sl_comm_unique_id": (C.c_int, [C.c_void_p]),
     "sl_comm_init_rank": (C.c_int, [_h, C.c_int, C.c_int, C.c_void_p]),
     "sl_allreduce_avg": (C.c_int, [_h]),

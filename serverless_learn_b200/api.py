@@ -191,5 +191,14 @@ class Replica:
         buf = C.create_string_buffer(uid, 128)
         self._ck(self._L.sl_comm_init_rank(self._h, nranks, rank, buf))
 
+    def peer_export(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._ck(self._L.sl_peer_export(self._h, buf))
+        return buf.raw
+
+    def peer_attach(self, nranks: int, rank: int, handles: bytes):
+        buf = C.create_string_buffer(handles, 64 * nranks) if handles else None
+        self._ck(self._L.sl_peer_attach(self._h, nranks, rank, buf))
+
     def allreduce_avg(self):
         self._ck(self._L.sl_allreduce_avg(self._h))

@@ -115,6 +115,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 // in a hung GPU.  kSpinLimit polls of >= ~300 cycles each is on the order of a second.
 // ------------------------------------------------------------------------------------
 constexpr uint32_t kSpinLimit = 1u << 22;
+constexpr uint32_t kPeerSpinLimit = 1u << 26;  // another GPU's kernel may start much later
 constexpr int kErrTimeoutMbar = 1;
 constexpr int kErrTimeoutPart = 2;
 constexpr int kErrTimeoutW = 3;
@@ -122,12 +123,14 @@ constexpr int kErrTimeoutW = 3;
 #ifndef SL_POLL_SLEEP
 #define SL_POLL_SLEEP 0
 #endif
-__device__ __forceinline__ bool spin_abort(uint32_t& spins, int* err, int code) {
+constexpr int kErrTimeoutPeer = 4;
+__device__ __forceinline__ bool spin_abort(uint32_t& spins, int* err, int code,
+                                           uint32_t limit = kSpinLimit) {
     ++spins;
     if (SL_POLL_SLEEP > 0) __nanosleep(SL_POLL_SLEEP);
     if ((spins & 1023u) == 0) {
         if (ld_vol_s32(err) != 0) return true;
-        if (spins >= kSpinLimit) {
+        if (spins >= limit) {
             atomicCAS(err, 0, code);
             return true;
         }
@@ -245,6 +248,14 @@ struct LrArgs {
     unsigned long long* acc;   // [3][krep][Fp] s64 gradient accumulators (zero at launch)
     unsigned* counter;     // arrivals; zero at launch
     double* wmaster;       // WS only: [grid][F] per-CTA fp64 master copies
+    // same-box data parallel (nranks > 1 or peers attached): one kernel per GPU, the kernels
+    // talk through peer-mapped memory over NVLink
+    int nranks, rank;      // nranks == 0: single-GPU exchange
+    uint4* peer_x[8];      // rank p's inbox [2][nranks][F] of {lo, flag, hi, flag} packets
+    unsigned long long* fin;   // [3][F] all-rank gradient totals of this GPU
+    unsigned* counter2;    // owner CTAs that have published their slice; zero at launch
+    unsigned xflag0;       // step s of this launch uses packet flag xflag0 + s + 1
+    int n_own;             // CTAs that own a 32-element slice of the vector
     unsigned long long* loss_fix;  // device [n_steps] s64 fixed-point loss sums (zero at launch) or nullptr
     double eta_over_b;
     int* err;              // 0 = ok; set by the watchdog
@@ -409,15 +420,79 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     if (spin_abort(spins, a.err, kErrTimeoutPart)) break;
                 }
                 asm volatile("fence.acq_rel.gpu;" ::: "memory");
-                if (XB) {
+                if (a.nranks == 0) {
+                    if (XB) {
+                        asm volatile("fence.proxy.async;" ::: "memory");
+                        const uint32_t wb = smem_u32(wfull);
+                        mbar_arrive_expect_tx(wb, (uint32_t)acc_stride * 8u);
+                        bulk_g2s_plain(smem_u32(gin), buf, (uint32_t)acc_stride * 8u, wb);
+                    } else {
+                        mbar_arrive(smem_u32(wfull));
+                    }
+                    dbg_stamp(a, s, 4);
+                }
+            }
+            if (XB && a.nranks > 0) {
+                // ---- cross-GPU stage, fused into the same kernel: the CTA that owns a 32-element
+                // slice sums this GPU's replicas of it, stores the sum into every peer's inbox over
+                // NVLink (16-byte data+flag packets), adds the peers' sums as they land, publishes
+                // the all-rank total locally.  s64 adds: exact, identical on every GPU.
+                __syncwarp();  // lane 0 has seen every local CTA's contribution (acquire above)
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                const unsigned xflag = a.xflag0 + (unsigned)s + 1u;
+                const size_t half = (size_t)(xflag & 1u) * (size_t)a.nranks * (size_t)F;
+                unsigned long long* fin = a.fin + (size_t)(s % 3) * F;
+                if (c < a.n_own) {
+                    const int e = c * 32 + lane;
+                    if (e < F) {
+                        long long tot = 0;
+                        for (int k = 0; k < KREP; ++k) tot += (long long)ld_relaxed_u64(buf + (size_t)k * Fp + e);
+                        const uint4 pkt = make_uint4((unsigned)((unsigned long long)tot & 0xffffffffu), xflag,
+                                                     (unsigned)((unsigned long long)tot >> 32), xflag);
+                        for (int p = 0; p < a.nranks; ++p)
+                            if (p != a.rank) st_vol_v4(a.peer_x[p] + half + (size_t)a.rank * F + e, pkt);
+                        const uint4* inbox = a.peer_x[a.rank] + half;
+                        for (int p0 = 0; p0 < a.nranks; p0 += 4) {  // 4 peers' packets in flight
+                            uint4 q[4];
+                            uint32_t spins = 0;
+                            for (;;) {
+                                bool ok = true;
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    const int p = p0 + k;
+                                    if (p < a.nranks && p != a.rank) {
+                                        q[k] = ld_vol_v4(inbox + (size_t)p * F + e);
+                                        ok = ok && q[k].y == xflag && q[k].w == xflag;
+                                    }
+                                }
+                                if (ok) break;
+                                if (spin_abort(spins, a.err, kErrTimeoutPeer, kPeerSpinLimit)) break;
+                            }
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const int p = p0 + k;
+                                if (p < a.nranks && p != a.rank)
+                                    tot += (long long)(((unsigned long long)q[k].z << 32) | (unsigned long long)q[k].x);
+                            }
+                        }
+                        fin[e] = (unsigned long long)tot;
+                    }
+                    __syncwarp();
+                    if (lane == 0) red_release_add_u32(a.counter2, 1u);
+                }
+                if (lane == 0) {
+                    const unsigned want2 = (unsigned)a.n_own * (unsigned)(s + 1);
+                    uint32_t spins = 0;
+                    while ((int)(ld_relaxed_u32(a.counter2) - want2) < 0) {
+                        if (spin_abort(spins, a.err, kErrTimeoutPeer, kPeerSpinLimit)) break;
+                    }
+                    asm volatile("fence.acq_rel.gpu;" ::: "memory");
                     asm volatile("fence.proxy.async;" ::: "memory");
                     const uint32_t wb = smem_u32(wfull);
-                    mbar_arrive_expect_tx(wb, (uint32_t)acc_stride * 8u);
-                    bulk_g2s_plain(smem_u32(gin), buf, (uint32_t)acc_stride * 8u, wb);
-                } else {
-                    mbar_arrive(smem_u32(wfull));
+                    mbar_arrive_expect_tx(wb, (uint32_t)F * 8u);
+                    bulk_g2s_plain(smem_u32(gin), fin, (uint32_t)F * 8u, wb);
+                    dbg_stamp(a, s, 4);
                 }
-                dbg_stamp(a, s, 4);
             }
             __syncwarp();
             // Everybody has contributed to step s, hence finished reading the buffer of
@@ -480,7 +555,8 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             if (!gv[ch]) continue;
             long long t[4] = {0, 0, 0, 0};
             if (XB) {
-                for (int k = 0; k < KREP; ++k) {
+                const int nrep = a.nranks > 0 ? 1 : KREP;  // multi-GPU: gin holds the one all-rank total
+                for (int k = 0; k < nrep; ++k) {
                     const longlong2* p = reinterpret_cast<const longlong2*>(gin + (size_t)k * Fp + gq[ch] * 4);
                     const longlong2 u = p[0], v = p[1];
                     t[0] += u.x; t[1] += u.y; t[2] += v.x; t[3] += v.y;

@@ -142,12 +142,20 @@ struct sl_handle {
     unsigned long long* dbg = nullptr;
     size_t dbg_words = 0;
     // info
+    long long k1_launches = 0;
     long long launches = 0, path_used = 0, variant_used = 0, grid_used = 0, ns_used = 0,
               smem_used = 0;
 
     // NCCL
     ncclComm_t comm = nullptr;
     int nranks = 1, rank = 0;
+    // peer-memory exchange of the fused multi-GPU kernel
+    unsigned char* xblock = nullptr;     // [inbox 2*8*F packets][fin 3*F u64]
+    size_t xblock_bytes = 0;
+    void* peer_base[8] = {nullptr};      // xblock of every rank as mapped here (own = xblock)
+    int peer_n = 0, peer_rank = 0;       // 0 = not attached
+    unsigned xflag_base = 0;
+    long long opt_sync_path = 0;         // 0 auto (fused when attached), 1 NCCL per step
 
     std::mutex mu;
     std::string err;
@@ -339,7 +347,8 @@ int ensure_exchange(sl_handle* h, const PersistPlan& plan) {
     return SL_OK;
 }
 
-int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_loss) {
+int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_loss,
+                bool fused_sync = false) {
     const Variant& v = kVariants[plan.variant];
     int rc = ensure_exchange(h, plan);
     if (rc) return rc;
@@ -374,8 +383,19 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         a.loss_fix = want_loss ? h->loss_fix + done : nullptr;
         // accumulators and the arrival counter start every launch at zero
         CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
-        CK(h, cudaMemsetAsync(h->counter, 0, 4, h->stream));
+        CK(h, cudaMemsetAsync(h->counter, 0, 128, h->stream));
         a.eta_over_b = h->eta / (double)h->B;
+        if (fused_sync) {
+            a.nranks = h->peer_n;
+            a.rank = h->peer_rank;
+            for (int p = 0; p < h->peer_n; ++p) a.peer_x[p] = reinterpret_cast<uint4*>(h->peer_base[p]);
+            a.fin = reinterpret_cast<unsigned long long*>(h->xblock + sizeof(uint4) * 2 * 8 * (size_t)h->F);
+            a.counter2 = h->counter + 16;
+            a.xflag0 = h->xflag_base;
+            a.n_own = (h->F + 31) / 32;
+            a.eta_over_b = h->eta / ((double)h->B * (double)h->peer_n);
+            h->xflag_base += (unsigned)n;
+        }
         a.err = h->d_err;
         a.dbg = nullptr;
         a.dbg_step = 0;
@@ -395,6 +415,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         CK(h, cudaLaunchCooperativeKernel(v.fn, dim3(plan.grid), dim3((v.ncw + 2) * 32), params,
                                           plan.smem, h->stream));
         h->launches++;
+        h->k1_launches++;
         h->step += n;
         done += n;
     }
@@ -404,7 +425,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         h->launches++;
         CK(h, cudaGetLastError());
     }
-    h->path_used = 1;
+    h->path_used = fused_sync ? 4 : 1;
     h->variant_used = plan.variant + 1;
     h->grid_used = plan.grid;
     h->ns_used = plan.args.ns;
@@ -449,7 +470,10 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     if (n_steps < 0) return fail(h, SL_EINVAL, "n_steps < 0");
     if (!h->shard_sealed || h->n_rows <= 0)
         return fail(h, SL_ESTATE, "no sealed shard with at least one row (sl_shard_end first)");
-    if (sync && !h->comm) return fail(h, SL_ESTATE, "sl_comm_init_rank has not been called");
+    if (sync && !h->comm && h->peer_n == 0)
+        return fail(h, SL_ESTATE, "neither sl_comm_init_rank nor sl_peer_attach has been called");
+    if (sync && !h->comm && (h->opt_sync_path != 0 || h->opt_path == 2))
+        return fail(h, SL_ESTATE, "the NCCL path needs sl_comm_init_rank");
     if (n_steps == 0) return SL_OK;
     DeviceGuard dg(h->device);
     int rc = ensure_loss_cap(h, (size_t)n_steps);
@@ -457,12 +481,26 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     PersistPlan plan;
     std::string why;
     bool persist = !sync && h->opt_path != 2 && plan_persist(h, &plan, &why);
+    bool fused = false;
+    if (sync && h->peer_n > 0 && h->opt_sync_path == 0 && h->opt_path != 2 && plan_persist(h, &plan, &why)) {
+        const Variant& v = kVariants[plan.variant];
+        fused = v.xb && (h->F + 31) / 32 <= plan.grid && h->peer_n <= 8;
+    }
     if (!sync && h->opt_path == 1 && !persist)
         return fail(h, SL_EINVAL, "persistent path requested but unavailable: %s", why.c_str());
     CK(h, cudaEventRecord(h->ev0, h->stream));
-    if (persist) {
-        rc = run_persist(h, plan, n_steps, loss_out != nullptr);
+    if (persist || fused) {
+        rc = run_persist(h, plan, n_steps, loss_out != nullptr, fused);
         if (rc) return rc;
+        if (fused && loss_out && h->comm && h->nranks > 1) {
+            // each rank evaluated the loss of its own rows: mean over ranks
+            int nrc = g_nccl.AllReduce(h->d_loss, h->d_loss, (size_t)n_steps, kNcclFloat64, kNcclSum,
+                                       h->comm, h->stream);
+            if (nrc != 0) return fail(h, SL_ENCCL, "ncclAllReduce(loss) failed (%d)", nrc);
+            slk::scale_kernel<<<(n_steps + 255) / 256, 256, 0, h->stream>>>(h->d_loss, n_steps,
+                                                                         1.0 / (double)h->nranks);
+            h->launches++;
+        }
     } else {
         rc = ensure_simple_scratch(h);
         if (rc) return rc;
@@ -568,6 +606,9 @@ int sl_destroy(sl_handle* h) {
     cudaFree(h->model); cudaFree(h->old); cudaFree(h->shard); cudaFree(h->in_buf);
     cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->d_loss); cudaFree(h->loss_fix);
     cudaFree(h->dbg);
+    for (int p = 0; p < h->peer_n; ++p)
+        if (p != h->peer_rank && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
+    cudaFree(h->xblock);
     cudaFree(h->resid); cudaFree(h->rowloss); cudaFree(h->gpart); cudaFree(h->gsum);
     if (h->h_in) cudaFreeHost(h->h_in);
     if (h->h_out) cudaFreeHost(h->h_out);
@@ -600,6 +641,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "debug_timeline") h->opt_dbg_step = value;
     else if (k == "ring_slots") h->opt_ring = value;
     else if (k == "krep") h->opt_krep = value;
+    else if (k == "sync_path") h->opt_sync_path = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
 }
@@ -609,6 +651,7 @@ long long sl_get_info(sl_handle* h, const char* key) {
     std::lock_guard<std::mutex> lk(h->mu);
     std::string k(key);
     if (k == "launches") return h->launches;
+    if (k == "k1_launches") return h->k1_launches;
     if (k == "path") return h->path_used;
     if (k == "variant") return h->variant_used;
     if (k == "grid") return h->grid_used;
@@ -618,6 +661,7 @@ long long sl_get_info(sl_handle* h, const char* key) {
     if (k == "step") return h->step;
     if (k == "n_rows") return h->n_rows;
     if (k == "nranks") return h->nranks;
+    if (k == "peers") return h->peer_n;
     if (k == "num_variants") return kNumVariants;
     return SL_EINVAL;
 }
@@ -908,6 +952,51 @@ int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128) {
                     g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
     h->nranks = nranks;
     h->rank = rank;
+    return SL_OK;
+}
+
+int sl_peer_export(sl_handle* h, void* handle64) {
+    if (!h || !handle64) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);
+    if (!h->xblock) {
+        const size_t bytes = sizeof(uint4) * 2 * 8 * (size_t)h->F + 8 * 3 * (size_t)h->F;
+        CK(h, cudaMalloc(&h->xblock, bytes));
+        CK(h, cudaMemset(h->xblock, 0, bytes));
+        h->xblock_bytes = bytes;
+    }
+    cudaIpcMemHandle_t ih;
+    CK(h, cudaIpcGetMemHandle(&ih, h->xblock));
+    static_assert(sizeof(ih) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle64, &ih, sizeof(ih));
+    return SL_OK;
+}
+
+int sl_peer_attach(sl_handle* h, int nranks, int rank, const void* handles) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks)
+        return fail(h, SL_EINVAL, "sl_peer_attach: 1 <= nranks <= 8 and 0 <= rank < nranks");
+    if (!h->xblock) return fail(h, SL_ESTATE, "sl_peer_attach before sl_peer_export");
+    if (h->peer_n) return fail(h, SL_ESTATE, "peers already attached");
+    if (nranks > 1 && !handles) return fail(h, SL_EINVAL, "handles is NULL");
+    DeviceGuard dg(h->device);
+    for (int p = 0; p < nranks; ++p) {
+        if (p == rank) { h->peer_base[p] = h->xblock; continue; }
+        cudaIpcMemHandle_t ih;
+        memcpy(&ih, static_cast<const unsigned char*>(handles) + 64 * (size_t)p, sizeof(ih));
+        void* ptr = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, ih, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(h, SL_ECUDA, "cudaIpcOpenMemHandle(rank %d) failed: %s", p, cudaGetErrorString(e));
+        }
+        h->peer_base[p] = ptr;
+    }
+    h->peer_n = nranks;
+    h->peer_rank = rank;
+    h->xflag_base = 0;
+    if (h->nranks == 1) { h->nranks = nranks; h->rank = rank; }
     return SL_OK;
 }
 

@@ -254,3 +254,50 @@ def test_lr_full_size_properties(sl):
         w2 = r.model()
     assert w_err(w1, w2) <= W_TOL
     assert float(np.max(np.abs(l1 - l2) / l2)) <= L_TOL
+
+
+def test_sync_mode_single_rank_equals_local_steps(sl, orc):
+    # sl_train_steps_sync with a 1-rank NCCL communicator: same numbers as the oracle; exercises
+    # the dlopen'd NCCL, the all-reduce of the gradient sum and the averaged update
+    n, F, B, steps, eta = 600, 128, 64, 9, 0.2
+    X, y = orc.synth(0, n, F)
+    w = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, steps, w, eta)
+    with sl.Replica(F, B, eta=eta) as r:
+        r.load_shard(X, y)
+        with pytest.raises(sl.SlError):
+            r.train_steps_sync(1)                      # no communicator yet
+        r.comm_init_rank(1, 0, sl.Replica.comm_unique_id())
+        lg = r.train_steps_sync(steps)
+        assert r.info("path") == 3
+        assert w_err(r.model(), w) <= W_TOL
+        assert float(np.max(np.abs(lg - lo) / lo)) <= L_TOL
+        r.allreduce_avg()                              # mean over one rank: unchanged
+        assert w_err(r.model(), w) <= W_TOL
+
+
+def test_fused_sync_path_single_rank(sl, orc):
+    # the in-kernel cross-GPU stage with nranks = 1 (no peer): owner slices, second counter
+    # and the load of the all-rank total are all exercised; numbers must equal plain steps
+    n, F, B, steps, eta = 900, 1024, 96, 11, 0.2
+    X, y = orc.synth(0, n, F)
+    w = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, steps, w, eta)
+    with sl.Replica(F, B, eta=eta) as r:
+        r.load_shard(X, y)
+        r.peer_export()
+        r.peer_attach(1, 0, b"")
+        assert r.info("peers") == 1
+        lg = np.concatenate([r.train_steps_sync(4), r.train_steps_sync(steps - 4)])
+        assert r.info("path") == 4
+        assert w_err(r.model(), w) <= W_TOL
+        assert float(np.max(np.abs(lg - lo) / lo)) <= L_TOL
+    with sl.Replica(F, B, eta=eta) as r2:              # bit-identical to the single-GPU kernel
+        r2.load_shard(X, y)
+        r2.train_steps(steps)
+        with sl.Replica(F, B, eta=eta) as r3:
+            r3.load_shard(X, y)
+            r3.peer_export()
+            r3.peer_attach(1, 0, b"")
+            r3.train_steps_sync(steps)
+            assert np.array_equal(r2.model(), r3.model())

@@ -1,0 +1,71 @@
+"""Multi-GPU parity + timing of sl_train_steps_sync (run under torchrun, one rank per GPU):
+the fused peer-memory kernel and the NCCL path against the oracle's W-worker sync loop.
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/sync_check.py
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import oracle  # noqa: E402  (checker)
+from serverless_learn_b200 import Replica  # noqa: E402
+
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr)
+dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+orc = oracle.Oracle()
+n, F, B, steps, eta = 1 << 14, 1024, 4096, 24, 0.1
+
+
+def gather_bytes(b: bytes, size: int) -> bytes:
+    t = torch.frombuffer(bytearray(b), dtype=torch.uint8).cuda()
+    out = [torch.zeros(size, dtype=torch.uint8, device="cuda") for _ in range(world)]
+    dist.all_gather(out, t)
+    return b"".join(bytes(o.cpu().numpy().tobytes()) for o in out)
+
+
+def bcast_bytes(b: bytes, size: int) -> bytes:
+    t = torch.zeros(size, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        t.copy_(torch.frombuffer(bytearray(b), dtype=torch.uint8))
+    dist.broadcast(t, 0)
+    return bytes(t.cpu().numpy().tobytes())
+
+
+shards = [orc.synth(k * n, n, F) for k in range(world)]
+w = np.zeros(F)
+lo = orc.lr_steps_sync([s[0] for s in shards], [s[1] for s in shards], B, 0, steps, w, eta)
+res = {}
+for mode in ("fused", "nccl"):
+    r = Replica(F, B, eta=eta, device=lr)
+    r.load_shard(*shards[rank])
+    r.comm_init_rank(world, rank, bcast_bytes(Replica.comm_unique_id() if rank == 0 else b"", 128))
+    if mode == "fused":
+        r.peer_attach(world, rank, gather_bytes(r.peer_export(), 64))
+    else:
+        r.set_option("sync_path", 1)
+    dist.barrier(); torch.cuda.synchronize()
+    lg = r.train_steps_sync(steps)
+    ew = float(np.max(np.abs(r.model() - w)) / np.max(np.abs(w)))
+    el = float(np.max(np.abs(lg - lo) / lo))
+    # timing on the big shard
+    r.shard_synth(1 << 20, row0=rank << 20)
+    r.train_steps_sync(64, want_loss=False)
+    dist.barrier(); torch.cuda.synchronize()
+    r.train_steps_sync(1024, want_loss=True)
+    ms = torch.tensor([r.last_train_ms()], device="cuda"); dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    res[mode] = (ew, el, r.info("path"), float(ms.item()) * 1e3 / 1024, r.model())
+    r.close()
+allw = [torch.zeros(F, dtype=torch.float64, device="cuda") for _ in range(world)]
+dist.all_gather(allw, torch.from_numpy(res["fused"][4]).cuda())
+same = all(bool(torch.equal(allw[0], x)) for x in allw)
+if rank == 0:
+    for mode, (ew, el, path, us, _) in res.items():
+        print(f"{mode:6s} world={world} path={path} w_err={ew:.2e} loss_err={el:.2e}  {us:.2f} us/step "
+              f"-> {world * B / us:.1f} M samples/s", flush=True)
+    print("fused: model bit-identical on all ranks:", same, flush=True)
+    assert res["fused"][0] <= 1e-5 and res["fused"][1] <= 1e-5 and res["nccl"][0] <= 1e-5 and same
+dist.destroy_process_group()
