@@ -57,6 +57,16 @@ def load() -> C.CDLL:
             raise RuntimeError(
                 f"{LIB_PATH} is missing: run `python -m serverless_learn_b200.build`. "
                 "There is no CPU fallback.")
+        if "SL_NCCL_LIB" not in os.environ:
+            # if PyTorch is installed, make the library pick the NCCL that torch bundles: a later
+            # `import torch` in the same process would otherwise meet a second libnccl.so.2
+            import importlib.util
+            spec = importlib.util.find_spec("nvidia")
+            for base in (list(spec.submodule_search_locations) if spec and spec.submodule_search_locations else []):
+                cand = os.path.join(base, "nccl", "lib", "libnccl.so.2")
+                if os.path.exists(cand):
+                    os.environ["SL_NCCL_LIB"] = cand
+                    break
         lib = C.CDLL(LIB_PATH)
         for name, (res, args) in _SIGS.items():
             fn = getattr(lib, name)

@@ -230,8 +230,11 @@ __device__ __forceinline__ float sigmoid_f(float z) { return 1.0f / (1.0f + expf
 // RS  rows per ring slot (divides R): one bulk copy and one mbarrier per slot
 // XB  exchange through shared memory + TMA (F small enough for smem staging); otherwise
 //     per-element red.global.add.u64 and direct loads (wide rows, where a step is long)
-// WS  (wide rows) fp32 weights live in shared memory and the fp64 master in a per-CTA
-//     global scratch instead of registers
+// WM  where the weights live.  0: fp32 copy and fp64 master of a thread's columns in its
+//     registers.  1 (wide rows): fp32 in shared memory, fp64 master in a per-CTA global scratch.
+//     2 (many row groups): fp32 in registers, ONE fp64 master per CTA in shared memory, updated
+//     by the first F/4 threads and broadcast through shared memory — frees 8 registers per
+//     column chunk, which is what lets 7 row groups hold a CTA's 28 rows of a step at once
 constexpr int kFixShift = 36;                       // gradient fixed point: 2^-36 units
 constexpr double kFixScale = 68719476736.0;         // 2^36
 constexpr double kFixInv = 1.0 / 68719476736.0;
@@ -266,7 +269,7 @@ struct LrArgs {
     int wpg;               // warps per row group = ceil(F/4/CH/32)
     int ns;                // ring slots (RS rows each)
     int row_bytes;         // 4*F
-    int off_bar, off_red, off_zy, off_gsm, off_gout, off_gin, off_wsm;  // smem offsets
+    int off_bar, off_red, off_zy, off_gsm, off_gout, off_gin, off_wsm, off_msm;  // smem offsets
     // diagnostics (sl_set_option "debug_timeline"): [4 steps][grid][16] time stamps
     unsigned long long* dbg;
     int dbg_step;
@@ -313,9 +316,11 @@ __device__ __forceinline__ void red_add_u64(unsigned long long* p, unsigned long
 // exact: scaling by 2^36 does not round in fp32, the conversion rounds once
 __device__ __forceinline__ long long to_fix(float v) { return __float2ll_rn(v * 68719476736.0f); }
 
-template <int CH, int R, int RS, int NCW, bool XB, bool WS>
+template <int CH, int R, int RS, int NCW, bool XB, int WM>
 __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrArgs a) {
     static_assert(R % RS == 0, "a sub-batch is a whole number of ring slots");
+    constexpr bool WS = WM == 1;  // fp32 weights read from smem in the dot, fp64 master in global
+    constexpr bool MS = WM == 2;  // fp32 weights in registers, fp64 master in smem (one copy per CTA)
     constexpr int SPB = R / RS;  // ring slots per sub-batch
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -331,7 +336,8 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     float* gsm = reinterpret_cast<float*>(smem + a.off_gsm);          // [RG-1][F]
     long long* gout = reinterpret_cast<long long*>(smem + a.off_gout);  // XB: [Fp]
     long long* gin = reinterpret_cast<long long*>(smem + a.off_gin);    // XB: [krep][Fp]
-    float* wsm = reinterpret_cast<float*>(smem + a.off_wsm);          // WS: [F]
+    float* wsm = reinterpret_cast<float*>(smem + a.off_wsm);          // WM != 0: [F] fp32 weights
+    double* msm = reinterpret_cast<double*>(smem + a.off_msm);        // WM == 2: [F] fp64 master
 
     const int WPG = a.wpg, RG = NCW / WPG, CT = WPG * 32;
     const int F = a.F, Fp = a.Fp, ns = a.ns, row_bytes = a.row_bytes, KREP = a.krep;
@@ -357,7 +363,12 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             mbar_init(smem_u32(&full[s]), 1);
             mbar_init(smem_u32(&empty[s]), WPG);
         }
-        mbar_init(smem_u32(gfull), XB ? WPG : WPG * 32);
+        {   // arrivals that complete "gradient staged": the warps (XB) or threads that write it
+            const int granules = F / 4;
+            const int comb_warps = RG > 1 ? (granules + 31) / 32 : WPG;
+            const int comb_threads = RG > 1 ? granules : WPG * 32;
+            mbar_init(smem_u32(gfull), XB ? comb_warps : comb_threads);
+        }
         mbar_init(smem_u32(wfull), 1);
         fence_mbar_init();
     }
@@ -522,14 +533,18 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     }
     // weights: fp64 master + fp32 working copy, per thread for its own columns
     constexpr int NW = WS ? 1 : CH;
+    constexpr int NM = WM == 0 ? CH : 1;
     float4 w[NW];
-    double wm[NW][4];
+    double wm[NM][4];
+    const int granules = F / 4;
+    const bool comb = RG > 1 ? tid < granules : rg == 0;  // threads that stage the CTA's gradient
     const uint32_t wsm_a = smem_u32(wsm);
     double* my_master = WS ? a.wmaster + (size_t)c * F : nullptr;
 #pragma unroll
     for (int ch = 0; ch < CH; ++ch) {
         if (!gv[ch]) {
-            if (!WS) { w[ch] = make_float4(0.f, 0.f, 0.f, 0.f); wm[ch][0] = wm[ch][1] = wm[ch][2] = wm[ch][3] = 0.0; }
+            if (!WS) w[ch] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (WM == 0) { wm[ch][0] = wm[ch][1] = wm[ch][2] = wm[ch][3] = 0.0; }
             continue;
         }
         const double* m = a.model + gq[ch] * 4;
@@ -542,14 +557,41 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             *reinterpret_cast<float4*>(wsm + gq[ch] * 4) = wf;
         } else {
             w[ch] = wf;
-            wm[ch][0] = m[0]; wm[ch][1] = m[1]; wm[ch][2] = m[2]; wm[ch][3] = m[3];
+            if (WM == 0) { wm[ch][0] = m[0]; wm[ch][1] = m[1]; wm[ch][2] = m[2]; wm[ch][3] = m[3]; }
         }
+    }
+    if (MS && tid < granules) {
+        const double* m = a.model + tid * 4;
+        msm[tid * 4 + 0] = m[0]; msm[tid * 4 + 1] = m[1]; msm[tid * 4 + 2] = m[2]; msm[tid * 4 + 3] = m[3];
     }
     if (WS) named_bar_sync(1, NCT);
 
     // apply the exact gradient total of step s to this thread's weights
     auto apply_total = [&](int s) {
         const unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
+        if (MS) {
+            if (tid < granules) {  // one updater per column chunk; XB is implied by the variant table
+                long long t[4] = {0, 0, 0, 0};
+                const int nrep = a.nranks > 0 ? 1 : KREP;
+                for (int k = 0; k < nrep; ++k) {
+                    const longlong2* p = reinterpret_cast<const longlong2*>(gin + (size_t)k * Fp + tid * 4);
+                    const longlong2 u = p[0], v = p[1];
+                    t[0] += u.x; t[1] += u.y; t[2] += v.x; t[3] += v.y;
+                }
+                double* mm = msm + tid * 4;
+                const double v0 = mm[0] - a.eta_over_b * ((double)t[0] * kFixInv);
+                const double v1 = mm[1] - a.eta_over_b * ((double)t[1] * kFixInv);
+                const double v2 = mm[2] - a.eta_over_b * ((double)t[2] * kFixInv);
+                const double v3 = mm[3] - a.eta_over_b * ((double)t[3] * kFixInv);
+                mm[0] = v0; mm[1] = v1; mm[2] = v2; mm[3] = v3;
+                *reinterpret_cast<float4*>(wsm + tid * 4) = make_float4((float)v0, (float)v1, (float)v2, (float)v3);
+            }
+            named_bar_sync(1, NCT);
+#pragma unroll
+            for (int ch = 0; ch < CH; ++ch)
+                if (gv[ch]) w[WS ? 0 : ch] = lds_v4(wsm_a + (uint32_t)gq[ch] * 16u);
+            return;
+        }
 #pragma unroll
         for (int ch = 0; ch < CH; ++ch) {
             if (!gv[ch]) continue;
@@ -577,7 +619,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     wf = make_float4((float)v0, (float)v1, (float)v2, (float)v3);
                     *reinterpret_cast<float4*>(wsm + gq[ch] * 4) = wf;
                 }
-            } else {
+            } else if (WM == 0) {
 #pragma unroll
                 for (int e = 0; e < 4; ++e) wm[ch][e] -= a.eta_over_b * ((double)t[e] * kFixInv);
                 w[ch] = make_float4((float)wm[ch][0], (float)wm[ch][1], (float)wm[ch][2], (float)wm[ch][3]);
@@ -721,43 +763,58 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
 
         // ---- combine row groups inside the CTA, hand the CTA's gradient to the exchange ----
         if (RG > 1) {
-            if (active && rg > 0) {
+            // every row group parks its partial; after the barrier the first F/4 threads each sum
+            // one column chunk over the groups (fixed order) — the combine is spread over warps
+            // instead of serialised on row group 0
+            if (active) {
 #pragma unroll
                 for (int ch = 0; ch < CH; ++ch)
                     if (gv[ch])
-                        *reinterpret_cast<float4*>(gsm + (size_t)(rg - 1) * F + gq[ch] * 4) = g[ch];
+                        *reinterpret_cast<float4*>(gsm + (size_t)rg * F + gq[ch] * 4) = g[ch];
             }
             named_bar_sync(1, NCT);
         }
-        if (rg == 0) {
+        if (comb) {
             unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch) {
-                if (!gv[ch]) continue;
-                float4 t = g[ch];
-                for (int k = 1; k < RG; ++k) {
-                    const float4 o =
-                        *reinterpret_cast<const float4*>(gsm + (size_t)(k - 1) * F + gq[ch] * 4);
-                    t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w;
+                int gqc;
+                float4 t;
+                if (RG > 1) {
+                    if (ch > 0) break;
+                    gqc = tid;
+                    t = *reinterpret_cast<const float4*>(gsm + gqc * 4);
+                    for (int k = 1; k < RG; ++k) {
+                        const float4 o = *reinterpret_cast<const float4*>(gsm + (size_t)k * F + gqc * 4);
+                        t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w;
+                    }
+                } else {
+                    if (!gv[ch]) continue;
+                    gqc = gq[ch];
+                    t = g[ch];
                 }
                 if (XB) {
-                    longlong2* p = reinterpret_cast<longlong2*>(gout + gq[ch] * 4);
+                    longlong2* p = reinterpret_cast<longlong2*>(gout + gqc * 4);
                     p[0] = make_longlong2(to_fix(t.x), to_fix(t.y));
                     p[1] = make_longlong2(to_fix(t.z), to_fix(t.w));
                 } else {
-                    red_add_u64(buf + gq[ch] * 4 + 0, (unsigned long long)to_fix(t.x));
-                    red_add_u64(buf + gq[ch] * 4 + 1, (unsigned long long)to_fix(t.y));
-                    red_add_u64(buf + gq[ch] * 4 + 2, (unsigned long long)to_fix(t.z));
-                    red_add_u64(buf + gq[ch] * 4 + 3, (unsigned long long)to_fix(t.w));
+                    red_add_u64(buf + gqc * 4 + 0, (unsigned long long)to_fix(t.x));
+                    red_add_u64(buf + gqc * 4 + 1, (unsigned long long)to_fix(t.y));
+                    red_add_u64(buf + gqc * 4 + 2, (unsigned long long)to_fix(t.z));
+                    red_add_u64(buf + gqc * 4 + 3, (unsigned long long)to_fix(t.w));
                 }
             }
-            if (XB) {
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(gfull));
-            } else {
+            if (!XB) {
                 __threadfence();  // this thread's adds are performed before the CTA signals
                 mbar_arrive(smem_u32(gfull));
             }
+        }
+        if (XB) {
+            // one arrival per warp that holds staging threads; the warp-wide sync sits outside
+            // the (possibly divergent) staging branch
+            const int comb_warps = RG > 1 ? (granules + 31) / 32 : WPG;
+            __syncwarp();
+            if (lane == 0 && warp < comb_warps) mbar_arrive(smem_u32(gfull));
         }
         if (tid == 0) dbg_stamp(a, s, 2);
         // off the critical path (the exchange is in flight): this step's loss
@@ -779,7 +836,12 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         apply_total(a.n_steps - 1);
     }
     // master weights back to global: all CTAs hold identical copies, CTA 0 writes
-    if (c == 0 && rg == 0) {
+    if (MS) {
+        if (c == 0 && tid < granules) {
+            double* m = a.model + tid * 4;
+            m[0] = msm[tid * 4]; m[1] = msm[tid * 4 + 1]; m[2] = msm[tid * 4 + 2]; m[3] = msm[tid * 4 + 3];
+        }
+    } else if (c == 0 && rg == 0) {
 #pragma unroll
         for (int ch = 0; ch < CH; ++ch) {
             if (!gv[ch]) continue;
@@ -787,7 +849,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             if (WS) {
                 const double* mm = my_master + gq[ch] * 4;
                 m[0] = mm[0]; m[1] = mm[1]; m[2] = mm[2]; m[3] = mm[3];
-            } else {
+            } else if (WM == 0) {
                 m[0] = wm[ch][0]; m[1] = wm[ch][1]; m[2] = wm[ch][2]; m[3] = wm[ch][3];
             }
         }

@@ -8,6 +8,7 @@
 #include <stdarg.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -47,9 +48,13 @@ const char* load_nccl() {
     if (g_nccl.lib) return nullptr;
     // a process that already imported torch has its bundled libnccl.so.2 mapped;
     // dlopen by soname returns that copy instead of loading a second NCCL.
-    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    // SL_NCCL_LIB names the copy to use when the process will ALSO load another library that
+    // bundles its own NCCL later (PyTorch does): two different libnccl.so.2 cannot coexist, so
+    // whoever comes first must pick the bundled one.
+    const char* names[] = {getenv("SL_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
     void* lib = nullptr;
     for (const char* n : names) {
+        if (!n || !*n) continue;
         lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
         if (lib) break;
     }
@@ -74,7 +79,7 @@ struct Variant {
 };
 #define SL_VARIANT(CH, R, RS, NCW, XB, WS) \
     Variant { CH, R, RS, NCW, XB, WS, \
-              (const void*)slk::lr_persist_kernel<CH, R, RS, NCW, (XB) != 0, (WS) != 0> }
+              (const void*)slk::lr_persist_kernel<CH, R, RS, NCW, (XB) != 0, WS> }
 // auto-selection takes the first variant wide enough for F
 const Variant kVariants[] = {
     SL_VARIANT(1, 16, 4, 8, 1, 0),    // 1: F <= 1024; measured best at F=1024, B/grid = 28
@@ -86,7 +91,7 @@ const Variant kVariants[] = {
     SL_VARIANT(4, 4, 2, 16, 0, 0),    // 7: F <= 8192, per-element exchange
     SL_VARIANT(8, 1, 1, 16, 0, 1),    // 8: F <= 16384, weights in shared memory
     SL_VARIANT(8, 2, 1, 8, 0, 1),     // 9: F <= 8192,  weights in shared memory
-    SL_VARIANT(4, 4, 4, 14, 1, 0),    // 10: F <= 1024 as 7 row groups of 2 warps x 4 rows
+    SL_VARIANT(4, 4, 4, 14, 1, 2),    // 10: F <= 1024 as 7 row groups of 2 warps x 4 rows: 28 rows in one pass
 };
 
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
@@ -294,11 +299,12 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     // fixed shared-memory regions after the ring
     const size_t red_b = sizeof(float) * 2 * v.ncw * v.r;
     const size_t zy_b = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
-    const size_t gsm_b = sizeof(float) * (size_t)std::max(0, rg - 1) * F;
+    const size_t gsm_b = rg > 1 ? sizeof(float) * (size_t)rg * F : 0;
     const size_t gout_b = v.xb ? 8 * (size_t)a.Fp : 0;
     const size_t gin_b = v.xb ? 8 * (size_t)a.Fp * a.krep : 0;
     const size_t wsm_b = v.ws ? sizeof(float) * (size_t)F : 0;
-    const size_t fixed = red_b + zy_b + gsm_b + gout_b + gin_b + wsm_b + 512;
+    const size_t msm_b = v.ws == 2 ? sizeof(double) * (size_t)F : 0;
+    const size_t fixed = red_b + zy_b + gsm_b + gout_b + gin_b + wsm_b + msm_b + 512;
     const size_t slot_b = (size_t)v.rs * a.row_bytes;
     if (slot_b > (1u << 20) - 16 || h->smem_optin < fixed + 16 + slot_b) {
         *why = "a ring slot does not fit in shared memory";
@@ -317,6 +323,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     off = align_up(off, 128); a.off_gout = (int)off; off += gout_b;
     off = align_up(off, 128); a.off_gin = (int)off;  off += gin_b;
     off = align_up(off, 16); a.off_wsm = (int)off;   off += wsm_b;
+    off = align_up(off, 16); a.off_msm = (int)off;   off += msm_b;
     p->smem = off;
     p->variant = vi;
     p->grid = grid;
@@ -334,7 +341,7 @@ int ensure_exchange(sl_handle* h, const PersistPlan& plan) {
         h->acc_bytes = need;
     }
     if (!h->counter) CK(h, cudaMalloc(&h->counter, 256));
-    if (v.ws) {
+    if (v.ws == 1) {
         const size_t wb = sizeof(double) * (size_t)plan.grid * h->F;
         if (h->wmaster_bytes < wb) {
             if (h->wmaster) cudaFree(h->wmaster);
