@@ -259,6 +259,7 @@ struct LrArgs {
     unsigned* counter2;    // owner CTAs that have published their slice; zero at launch
     unsigned xflag0;       // step s of this launch uses packet flag xflag0 + s + 1
     int n_own;             // CTAs that own a 32-element slice of the vector
+    int direct_total;      // 1: threads read the gradient total straight from L2 instead of a TMA load into smem
     unsigned long long* loss_fix;  // device [n_steps] s64 fixed-point loss sums (zero at launch) or nullptr
     double eta_over_b;
     int* err;              // 0 = ok; set by the watchdog
@@ -305,6 +306,11 @@ __device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned* p) {
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
     unsigned long long v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ ulonglong2 ld_relaxed_v2u64(const unsigned long long* p) {
+    ulonglong2 v;
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void red_release_add_u32(unsigned* p, unsigned v) {
@@ -432,7 +438,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                 }
                 asm volatile("fence.acq_rel.gpu;" ::: "memory");
                 if (a.nranks == 0) {
-                    if (XB) {
+                    if (XB && !a.direct_total) {
                         asm volatile("fence.proxy.async;" ::: "memory");
                         const uint32_t wb = smem_u32(wfull);
                         mbar_arrive_expect_tx(wb, (uint32_t)acc_stride * 8u);
@@ -596,7 +602,22 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         for (int ch = 0; ch < CH; ++ch) {
             if (!gv[ch]) continue;
             long long t[4] = {0, 0, 0, 0};
-            if (XB) {
+            if (XB && a.direct_total && a.nranks == 0) {
+                ulonglong2 u[4], v[4];  // KREP <= 4; all loads in flight, one L2 round trip
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (k < KREP) {
+                        const unsigned long long* p = buf + (size_t)k * Fp + gq[ch] * 4;
+                        u[k] = ld_relaxed_v2u64(p);
+                        v[k] = ld_relaxed_v2u64(p + 2);
+                    }
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (k < KREP) {
+                        t[0] += (long long)u[k].x; t[1] += (long long)u[k].y;
+                        t[2] += (long long)v[k].x; t[3] += (long long)v[k].y;
+                    }
+            } else if (XB) {
                 const int nrep = a.nranks > 0 ? 1 : KREP;  // multi-GPU: gin holds the one all-rank total
                 for (int k = 0; k < nrep; ++k) {
                     const longlong2* p = reinterpret_cast<const longlong2*>(gin + (size_t)k * Fp + gq[ch] * 4);

@@ -142,7 +142,7 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0;
     unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
     size_t dbg_words = 0;
@@ -392,6 +392,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 128, h->stream));
         a.eta_over_b = h->eta / (double)h->B;
+        a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && plan.args.krep <= 4) ? 1 : 0;
         if (fused_sync) {
             a.nranks = h->peer_n;
             a.rank = h->peer_rank;
@@ -648,6 +649,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "debug_timeline") h->opt_dbg_step = value;
     else if (k == "ring_slots") h->opt_ring = value;
     else if (k == "krep") h->opt_krep = value;
+    else if (k == "direct_total") h->opt_direct = value;
     else if (k == "sync_path") h->opt_sync_path = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;

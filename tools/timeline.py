@@ -9,14 +9,15 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from serverless_learn_b200 import Replica  # noqa: E402
 
 variant = int(sys.argv[1]) if len(sys.argv) > 1 else 2
-F = 1024
+F = int(sys.argv[3]) if len(sys.argv) > 3 else 1024
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+ROWS = int(sys.argv[4]) if len(sys.argv) > 4 else 1 << 20
 with Replica(F, B) as r:
-    r.shard_synth(1 << 20)
+    r.shard_synth(ROWS)
     r.set_option("variant", variant)
-    r.train_steps(64, want_loss=False)
-    r.set_option("debug_timeline", 100)
-    r.train_steps(256, want_loss=False)
+    r.train_steps(8, want_loss=False)
+    r.set_option("debug_timeline", 10)
+    r.train_steps(32, want_loss=False)
     G = r.info("grid")
     buf = np.zeros(4 * G * 16, dtype=np.uint64)
     rc = r._L.sl_debug_read(r._h, buf.ctypes.data_as(C.POINTER(C.c_ulonglong)), buf.size)
@@ -26,7 +27,7 @@ names = ["P0 step start", "P1 compute done", "P2 gradient staged", "P3 counter b
 order = [0, 5, 1, 2, 6, 7, 3, 4]
 for s in range(1, 3):
     g0 = t[s, :, 0, 1].min()
-    print(f"--- step {100 + s}: globaltimer ns relative to earliest CTA step start (min / median / max over CTAs)")
+    print(f"--- step {10 + s}: globaltimer ns relative to earliest CTA step start (min / median / max over CTAs)")
     for p in order:
         v = t[s, :, p, 1] - g0
         print(f"  {names[p]:24s} {v.min():7d} {int(np.median(v)):7d} {v.max():7d}")
