@@ -132,6 +132,13 @@ int sl_set_state(sl_handle* h, const double* model, const double* old, int n);
  * call sl_comm_init_rank on every rank.  NCCL is resolved with dlopen at that
  * point.  sl_allreduce_avg: model <- mean over ranks of model (one ncclAllReduce).
  * sl_train_steps_sync: n_steps of { local gradient; all-reduce; update }. */
+/* Reference-faithful pairwise exchange between two replicas of ONE process (one per GPU, or two
+ * on the same GPU): the whole round of periodically_gossip (src/worker.cc:194-219) and of the
+ * peer's ExchangeUpdates handler (src/worker.cc:81-100) in one kernel on the callee's GPU, which
+ * reads and writes the initiator's state through peer-mapped memory (NVLink) — no host staging,
+ * no wire.  Bit-exact with sl_delta_snapshot -> sl_merge -> sl_apply_reply. */
+int sl_gossip_p2p(sl_handle* initiator, sl_handle* callee);
+
 /* Fused path (preferred): sl_peer_export yields a 64-byte IPC handle of this replica's inbox;
  * gather the handles of all ranks (rank order) and pass them to sl_peer_attach on every rank
  * (1 <= nranks <= 8, one process per GPU, same box).  sl_train_steps_sync then runs ALL steps

@@ -36,6 +36,7 @@ _SIGS = {
     "sl_get_model": (C.c_int, [_h, _dp, C.c_int]),
     "sl_get_old": (C.c_int, [_h, _dp, C.c_int]),
     "sl_set_state": (C.c_int, [_h, _dp, _dp, C.c_int]),
+    "sl_gossip_p2p": (C.c_int, [_h, _h]),
     "sl_peer_export": (C.c_int, [_h, C.c_void_p]),
     "sl_peer_attach": (C.c_int, [_h, C.c_int, C.c_int, C.c_void_p]),
     "sl_comm_unique_id": (C.c_int, [C.c_void_p]),

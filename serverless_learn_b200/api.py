@@ -191,6 +191,10 @@ class Replica:
         buf = C.create_string_buffer(uid, 128)
         self._ck(self._L.sl_comm_init_rank(self._h, nranks, rank, buf))
 
+    def gossip_p2p(self, callee: "Replica") -> None:
+        """One gossip round with `callee` (this replica initiates), entirely on the GPUs."""
+        self._ck(self._L.sl_gossip_p2p(self._h, callee._h))
+
     def peer_export(self) -> bytes:
         buf = C.create_string_buffer(64)
         self._ck(self._L.sl_peer_export(self._h, buf))

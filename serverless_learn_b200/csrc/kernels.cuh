@@ -1047,6 +1047,27 @@ __global__ void apply_kernel(double* __restrict__ model, double* __restrict__ ol
     }
 }
 
+// One whole gossip round between two replicas in ONE kernel (src/worker.cc:194-219 on the
+// initiator A, src/worker.cc:81-100 on the callee B): A's state is read and written through
+// peer-mapped pointers over NVLink when A lives on another GPU.  Same arithmetic, same order:
+//   d = A.model - A.old ; B.model += l*d ; reply = B.model - B.old ; B.old = B.model ;
+//   A.model += l*reply ; A.old = A.model
+__global__ void gossip_p2p_kernel(double* __restrict__ a_model, double* __restrict__ a_old,
+                                  double* __restrict__ b_model, double* __restrict__ b_old, int n,
+                                  double lambda_a, double lambda_b) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double am = a_model[i], ao = a_old[i];
+    const double d = __dsub_rn(am, ao);                          // src/worker.cc:207
+    const double bm = __dadd_rn(b_model[i], __dmul_rn(lambda_b, d));   // :92
+    const double reply = __dsub_rn(bm, b_old[i]);                // :93
+    b_model[i] = bm;
+    b_old[i] = bm;                                               // :96
+    const double am2 = __dadd_rn(am, __dmul_rn(lambda_a, reply));      // :162
+    a_model[i] = am2;
+    a_old[i] = am2;                                              // :215
+}
+
 __global__ void tick_kernel(double* __restrict__ model, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) model[i] = __dadd_rn(model[i], 1.0);      // src/worker.cc:226

@@ -48,10 +48,15 @@ int WorkerCore::GossipOnce(Directory& dir) {
         lucky_worker_index = rand() % (int)peer_list_.size();  // :200
         lucky_worker_addr = peer_list_[lucky_worker_index];    // :201
     }
-    std::vector<double> update((size_t)D_), update_back((size_t)D_);
-    if (sl_delta_snapshot(h_, update.data(), D_) != 0) return -2;  // :205-208
     WorkerCore* peer = dir.find(lucky_worker_addr);                // :210-211
     if (!peer) return -1;                                          // R7: unreachable partner
+    if (peer != this) {
+        // both replicas live in this process: the whole round (:205-215 here, :85-96 on the peer)
+        // runs as one kernel over peer-mapped memory, bit-exact with the staged path below
+        return sl_gossip_p2p(h_, peer->h_) == 0 ? lucky_worker_index : -2;
+    }
+    std::vector<double> update((size_t)D_), update_back((size_t)D_);
+    if (sl_delta_snapshot(h_, update.data(), D_) != 0) return -2;  // :205-208
     // WorkerStub::ExchangeUpdates, :145-172.  The reference applies the reply before it looks
     // at the status (:155-166); here a failed call skips the apply (R7).
     if (!peer->ExchangeUpdates(update.data(), D_, update_back.data(), D_)) return -1;

@@ -964,6 +964,40 @@ int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128) {
     return SL_OK;
 }
 
+int sl_gossip_p2p(sl_handle* initiator, sl_handle* callee) {
+    if (!initiator || !callee) return SL_EINVAL;
+    if (initiator == callee) return fail(initiator, SL_EINVAL, "sl_gossip_p2p: a replica cannot gossip with itself here");
+    // lock both handles in address order (two threads may gossip in opposite directions)
+    sl_handle* first = initiator < callee ? initiator : callee;
+    sl_handle* second = initiator < callee ? callee : initiator;
+    std::lock_guard<std::mutex> l1(first->mu);
+    std::lock_guard<std::mutex> l2(second->mu);
+    if (initiator->D != callee->D)
+        return fail(initiator, SL_EINVAL, "sl_gossip_p2p: model lengths differ (%d vs %d)", initiator->D, callee->D);
+    DeviceGuard dg(callee->device);
+    if (initiator->device != callee->device) {
+        int can = 0;
+        CK(initiator, cudaDeviceCanAccessPeer(&can, callee->device, initiator->device));
+        if (!can) return fail(initiator, SL_ECUDA, "GPU %d cannot map GPU %d's memory", callee->device, initiator->device);
+        cudaError_t e = cudaDeviceEnablePeerAccess(initiator->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+            return fail(initiator, SL_ECUDA, "cudaDeviceEnablePeerAccess failed: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+    }
+    // the initiator's own stream must be idle before another GPU touches its state
+    {
+        DeviceGuard dgi(initiator->device);
+        CK(initiator, cudaStreamSynchronize(initiator->stream));
+    }
+    const int n = callee->D;
+    slk::gossip_p2p_kernel<<<(n + 127) / 128, 128, 0, callee->stream>>>(
+        initiator->model, initiator->old, callee->model, callee->old, n, initiator->lambda, callee->lambda);
+    callee->launches++;
+    CK(callee, cudaGetLastError());
+    CK(callee, cudaStreamSynchronize(callee->stream));
+    return SL_OK;
+}
+
 int sl_peer_export(sl_handle* h, void* handle64) {
     if (!h || !handle64) return SL_EINVAL;
     std::lock_guard<std::mutex> lk(h->mu);

@@ -301,3 +301,25 @@ def test_fused_sync_path_single_rank(sl, orc):
             r3.peer_attach(1, 0, b"")
             r3.train_steps_sync(steps)
             assert np.array_equal(r2.model(), r3.model())
+
+
+@pytest.mark.parametrize("n", [1, 7, 1024, 16384])
+def test_gossip_p2p_bit_exact(sl, orc, n):
+    # one-kernel gossip round == delta -> merge -> apply through the host, == the oracle.
+    # Uses a second GPU for the initiator when the box has one (peer-mapped state over NVLink).
+    import torch
+    dev_a = 1 if torch.cuda.device_count() > 1 else 0
+    rng = np.random.default_rng(n)
+    am, ao, bm, bo = (rng.standard_normal(n) * 10.0 ** rng.integers(-6, 6, n) for _ in range(4))
+    with sl.Replica(n, 1, device=dev_a, lam=0.5) as A, sl.Replica(n, 1, device=0, lam=0.25) as Bn:
+        A.set_state(am, ao)
+        Bn.set_state(bm, bo)
+        for _ in range(2):
+            A.gossip_p2p(Bn)
+            d = orc.delta(am, ao)
+            rep = orc.merge_callee(bm, bo, d, 0.25)
+            orc.apply_reply(am, ao, rep, 0.5)
+            assert np.array_equal(A.model(), am) and np.array_equal(A.old(), am)
+            assert np.array_equal(Bn.model(), bm) and np.array_equal(Bn.old(), bo)
+        with pytest.raises(sl.SlError):
+            A.gossip_p2p(A)
