@@ -258,7 +258,8 @@ struct LrArgs {
     unsigned long long* fin;   // [3][F] all-rank gradient totals of this GPU
     unsigned* counter2;    // owner CTAs that have published their slice; zero at launch
     unsigned xflag0;       // step s of this launch uses packet flag xflag0 + s + 1
-    int n_own;             // CTAs that own a 32-element slice of the vector
+    int n_own;             // CTAs that own a slice of the vector in the cross-GPU stage
+    int xslice;            // elements per slice (32 in lr_persist_kernel)
     int direct_total;      // 1: threads read the gradient total straight from L2 instead of a TMA load into smem
     unsigned long long* loss_fix;  // device [n_steps] s64 fixed-point loss sums (zero at launch) or nullptr
     double eta_over_b;

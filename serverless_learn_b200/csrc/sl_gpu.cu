@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "kernels_wide.cuh"
 
 namespace {
 
@@ -74,13 +75,14 @@ const char* load_nccl() {
 
 // ---- persistent-kernel variants -----------------------------------------------------
 struct Variant {
-    int ch, r, rs, ncw, xb, ws;
+    int ch, r, rs, ncw, xb, ws, kind;  // kind 0: lr_persist_kernel, 1: lr_wide_kernel
     const void* fn;
 };
 #define SL_VARIANT(CH, R, RS, NCW, XB, WS) \
-    Variant { CH, R, RS, NCW, XB, WS, \
+    Variant { CH, R, RS, NCW, XB, WS, 0, \
               (const void*)slk::lr_persist_kernel<CH, R, RS, NCW, (XB) != 0, WS> }
-// auto-selection takes the first variant wide enough for F
+#define SL_WIDE(CH, NCW) \
+    Variant { CH, 1, 1, NCW, 1, 1, 1, (const void*)slk::lr_wide_kernel<CH, NCW> }
 const Variant kVariants[] = {
     SL_VARIANT(1, 16, 4, 8, 1, 0),    // 1: F <= 1024; measured best at F=1024, B/grid = 28
     SL_VARIANT(1, 16, 4, 16, 1, 0),   // 2: F <= 2048; two row groups of 16 rows
@@ -92,8 +94,12 @@ const Variant kVariants[] = {
     SL_VARIANT(8, 1, 1, 16, 0, 1),    // 8: F <= 16384, weights in shared memory
     SL_VARIANT(8, 2, 1, 8, 0, 1),     // 9: F <= 8192,  weights in shared memory
     SL_VARIANT(4, 4, 4, 14, 1, 2),    // 10: F <= 1024 as 7 row groups of 2 warps x 4 rows: 28 rows in one pass
+    SL_WIDE(10, 14),                  // 11: F <= 17920, wide-row kernel, 14+2 warps = 128 registers/thread
+    SL_WIDE(5, 14),                   // 12: F <= 8960,  wide-row kernel
+    SL_WIDE(2, 16),                   // 13: F <= 4096,  wide-row kernel
 };
-
+// auto-selection: the first of these that is wide enough for F
+const int kAutoOrder[] = {1, 2, 6, 12, 11};
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 }  // namespace
@@ -277,7 +283,8 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
             return false;
         }
     } else {
-        for (int i = 0; i < kNumVariants; ++i) {
+        for (int k : kAutoOrder) {
+            const int i = k - 1;
             if (granules <= kVariants[i].ch * 32 * kVariants[i].ncw) { vi = i; break; }
         }
         if (vi < 0) { *why = "F too wide for the persistent kernel"; return false; }
@@ -292,6 +299,31 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     a.Fp = F;
     a.zy_rows = (((h->B + grid - 1) / grid + v.r - 1) / v.r) * v.r;
     a.krep = !v.xb ? 1 : (F <= 1024 ? 4 : (F <= 2048 ? 2 : 1));
+    a.xslice = 32;
+    if (v.kind == 1) {
+        a.krep = 1;
+        a.row_bytes = 4 * F;
+        a.zy_rows = (h->B + grid - 1) / grid;
+        a.xslice = 32 * ((F + 32 * grid - 1) / (32 * grid));
+        const size_t red_w = sizeof(float) * 2 * v.ncw;
+        const size_t zy_w = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
+        const size_t gout_w = 8 * (size_t)v.ncw * 32 * 4;
+        const size_t fixed_w = red_w + zy_w + gout_w + 512;
+        if (h->smem_optin < fixed_w + 16 + (size_t)a.row_bytes) { *why = "row does not fit in shared memory"; return false; }
+        size_t nsw = (h->smem_optin - fixed_w) / ((size_t)a.row_bytes + 16);
+        nsw = std::min<size_t>(nsw, 64);
+        if (h->opt_ring > 0) nsw = std::min<size_t>(nsw, (size_t)h->opt_ring);
+        a.ns = (int)nsw;
+        size_t offw = (size_t)a.ns * a.row_bytes;
+        offw = align_up(offw, 16); a.off_bar = (int)offw;   offw += 8 * (2 * nsw + 3);
+        offw = align_up(offw, 16); a.off_red = (int)offw;   offw += red_w;
+        offw = align_up(offw, 16); a.off_zy = (int)offw;    offw += zy_w;
+        offw = align_up(offw, 128); a.off_gout = (int)offw; offw += gout_w;
+        p->smem = offw;
+        p->variant = vi;
+        p->grid = grid;
+        return true;
+    }
     if (v.xb && h->opt_krep > 0) a.krep = (int)h->opt_krep;
     a.wpg = (granules + v.ch * 32 - 1) / (v.ch * 32);
     a.row_bytes = 4 * F;
@@ -392,7 +424,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 128, h->stream));
         a.eta_over_b = h->eta / (double)h->B;
-        a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && plan.args.krep <= 4) ? 1 : 0;
+        a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && kVariants[plan.variant].kind == 0 && plan.args.krep <= 4) ? 1 : 0;
         if (fused_sync) {
             a.nranks = h->peer_n;
             a.rank = h->peer_rank;
@@ -400,7 +432,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
             a.fin = reinterpret_cast<unsigned long long*>(h->xblock + sizeof(uint4) * 2 * 8 * (size_t)h->F);
             a.counter2 = h->counter + 16;
             a.xflag0 = h->xflag_base;
-            a.n_own = (h->F + 31) / 32;
+            a.n_own = (h->F + plan.args.xslice - 1) / plan.args.xslice;
             a.eta_over_b = h->eta / ((double)h->B * (double)h->peer_n);
             h->xflag_base += (unsigned)n;
         }
@@ -492,7 +524,7 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     bool fused = false;
     if (sync && h->peer_n > 0 && h->opt_sync_path == 0 && h->opt_path != 2 && plan_persist(h, &plan, &why)) {
         const Variant& v = kVariants[plan.variant];
-        fused = v.xb && (h->F + 31) / 32 <= plan.grid && h->peer_n <= 8;
+        fused = v.xb && (h->F + plan.args.xslice - 1) / plan.args.xslice <= plan.grid && h->peer_n <= 8;
     }
     if (!sync && h->opt_path == 1 && !persist)
         return fail(h, SL_EINVAL, "persistent path requested but unavailable: %s", why.c_str());

@@ -178,7 +178,7 @@ def test_lr_golden_cases(sl, orc, name, path):
     assert w_err(wg, GOLD[f"{name}_w"]) <= W_TOL
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8, 9, 10])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13])
 @pytest.mark.parametrize("shape", [(300, 64, 48), (2000, 1024, 256), (700, 260, 100)])
 def test_lr_all_variants(sl, orc, variant, shape):
     n, F, B = shape

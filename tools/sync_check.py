@@ -17,7 +17,10 @@ rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os
 torch.cuda.set_device(lr)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
 orc = oracle.Oracle()
-n, F, B, steps, eta = 1 << 14, 1024, 4096, 24, 0.1
+F = int(os.environ.get("SL_F", 1024))
+B = int(os.environ.get("SL_B", 4096))
+n, steps, eta = max(2 * B, (1 << 24) // F), 24, 0.1
+BIG = int(os.environ.get("SL_BIG", 1 << 20))
 
 
 def gather_bytes(b: bytes, size: int) -> bytes:
@@ -52,7 +55,7 @@ for mode in ("fused", "nccl"):
     ew = float(np.max(np.abs(r.model() - w)) / np.max(np.abs(w)))
     el = float(np.max(np.abs(lg - lo) / lo))
     # timing on the big shard
-    r.shard_synth(1 << 20, row0=rank << 20)
+    r.shard_synth(BIG, row0=rank * BIG)
     r.train_steps_sync(64, want_loss=False)
     dist.barrier(); torch.cuda.synchronize()
     r.train_steps_sync(1024, want_loss=True)
