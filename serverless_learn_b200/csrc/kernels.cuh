@@ -260,6 +260,7 @@ struct LrArgs {
     unsigned xflag0;       // step s of this launch uses packet flag xflag0 + s + 1
     int n_own;             // CTAs that own a slice of the vector in the cross-GPU stage
     int xslice;            // elements per slice (32 in lr_persist_kernel)
+    int hold_refills;      // 1: the producer re-arms slots only after the step's reduction is released
     int direct_total;      // 1: threads read the gradient total straight from L2 instead of a TMA load into smem
     unsigned long long* loss_fix;  // device [n_steps] s64 fixed-point loss sums (zero at launch) or nullptr
     double eta_over_b;
@@ -338,6 +339,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     uint64_t* empty = full + a.ns;                                     // [ns]
     uint64_t* gfull = empty + a.ns;                                    // [1] gradient staged
     uint64_t* wfull = gfull + 1;                                       // [1] total received
+    uint64_t* rgo = wfull + 1;                                         // [1] reduction released (gates refills)
     float* red = reinterpret_cast<float*>(smem + a.off_red);          // [2][NCW][R]
     float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);          // [2][zy_rows] (z, y) per row
     float* gsm = reinterpret_cast<float*>(smem + a.off_gsm);          // [RG-1][F]
@@ -377,6 +379,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             mbar_init(smem_u32(gfull), XB ? comb_warps : comb_threads);
         }
         mbar_init(smem_u32(wfull), 1);
+        mbar_init(smem_u32(rgo), 1);
         fence_mbar_init();
     }
     __syncthreads();
@@ -387,8 +390,20 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             const uint64_t pol = policy_evict_first();
             uint32_t slot = 0, phase = 0;
             long long mb = mb0;
+            // hold_refills: a slot freed during step t is re-armed only once step t's gradient
+            // reduction has been released — the HBM refill burst otherwise shares L2 with the
+            // 148 CTAs' reductions and stretches the release by ~0.8 us
+            uint32_t pos = 0;        // position of the slot being issued in this CTA's stream
+            int gated = -1;          // last step whose release has been awaited
             for (int s = 0; s < a.n_steps; ++s) {
-                for (int q = 0; q < nsl_c; ++q) {
+                for (int q = 0; q < nsl_c; ++q, ++pos) {
+                    if (a.hold_refills && pos >= (uint32_t)ns) {
+                        const int freed_in = (int)((pos - (uint32_t)ns) / (uint32_t)nsl_c);
+                        while (gated < freed_in) {
+                            ++gated;
+                            mbar_wait(smem_u32(rgo), (uint32_t)gated & 1u, a.err);
+                        }
+                    }
                     mbar_wait(smem_u32(&empty[slot]), phase ^ 1u, a.err);
                     const int rc = min(RS, nrows_c - q * RS);
                     const uint32_t fb = smem_u32(&full[slot]);
@@ -431,6 +446,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     asm volatile("fence.proxy.async;" ::: "memory");
                 }
                 red_release_add_u32(a.counter, 1u);
+                mbar_arrive(smem_u32(rgo));  // the producer may refill what step s freed
                 dbg_stamp(a, s, 3);
                 const unsigned want = (unsigned)G * (unsigned)(s + 1);
                 uint32_t spins = 0;

@@ -148,7 +148,7 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0;
     unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
     size_t dbg_words = 0;
@@ -348,7 +348,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     if (ns < 1) { *why = "no ring slot fits"; return false; }
     a.ns = (int)ns;
     size_t off = (size_t)a.ns * slot_b;
-    off = align_up(off, 16); a.off_bar = (int)off;   off += 8 * (2 * ns + 2);
+    off = align_up(off, 16); a.off_bar = (int)off;   off += 8 * (2 * ns + 3);
     off = align_up(off, 16); a.off_red = (int)off;   off += red_b;
     off = align_up(off, 16); a.off_zy = (int)off;    off += zy_b;
     off = align_up(off, 16); a.off_gsm = (int)off;   off += gsm_b;
@@ -424,6 +424,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 128, h->stream));
         a.eta_over_b = h->eta / (double)h->B;
+        a.hold_refills = h->opt_hold != 0 ? 1 : 0;
         a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && kVariants[plan.variant].kind == 0 && plan.args.krep <= 4) ? 1 : 0;
         if (fused_sync) {
             a.nranks = h->peer_n;
@@ -682,6 +683,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "ring_slots") h->opt_ring = value;
     else if (k == "krep") h->opt_krep = value;
     else if (k == "direct_total") h->opt_direct = value;
+    else if (k == "hold_refills") h->opt_hold = value;
     else if (k == "sync_path") h->opt_sync_path = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
