@@ -45,6 +45,14 @@ long long slr_file_server_chunk(slr_file_server* fs, long long k, const void** d
 int slr_file_server_do_push(slr_file_server* fs, slr_directory* d, const char* recipient_addr,
                             unsigned file_num);
 int slr_file_server_check_up(slr_file_server* fs); /* :122-130, no-op, returns 1 */
+/* Beyond the reference (it only knows file 0): further files addressed by Push.file_num
+ * (proto:36-39).  File k > 0 = a training shard in the stream layout sl_shard_* expects, rows
+ * [row0, row0+n_rows) of the synthetic matrix; unknown numbers keep the reference's error. */
+int slr_file_server_add_synthetic_shard(slr_file_server* fs, unsigned file_num, unsigned long long row0,
+                                        unsigned long long n_rows, unsigned F, unsigned long long seed);
+long long slr_file_server_file_length_of(slr_file_server* fs, unsigned file_num); /* -1 unknown */
+long long slr_file_server_chunk_of(slr_file_server* fs, unsigned file_num, long long k,
+                                   const void** data);
 
 /* ---- master (src/master.cc) ------------------------------------------------------------- */
 int slr_master_create(int device, int D, int B, double eta, double lambda, slr_master** out);
@@ -61,6 +69,8 @@ int slr_master_exchange_updates_wire(slr_master* m, const void* in, long in_len,
 /* one round of periodically_request_pushes (:220-237): file 0 to every registered worker, in
  * registration order; returns the number of successful pushes */
 int slr_master_request_pushes(slr_master* m, slr_file_server* fs, slr_directory* d);
+/* the same round with a shard assignment: the i-th registered worker gets file i+1 */
+int slr_master_request_pushes_sharded(slr_master* m, slr_file_server* fs, slr_directory* d);
 /* one round of periodically_do_checkups (:240-266): every worker receives the full peer list */
 int slr_master_do_checkups(slr_master* m, slr_file_server* fs, slr_directory* d);
 

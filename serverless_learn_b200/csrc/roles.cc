@@ -92,14 +92,58 @@ long long FileServerCore::chunk(long long k, const void** data) const {
     return left < kChunkSize ? left : kChunkSize;
 }
 
+namespace {
+inline uint64_t splitmix64(uint64_t x) {
+    uint64_t z = x + 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+}  // namespace
+
+bool FileServerCore::AddSyntheticShard(uint32_t file_num, uint64_t row0, uint64_t n_rows, uint32_t F,
+                                       uint64_t seed) {
+    if (file_num == 0 || n_rows == 0 || F == 0) return false;  // file 0 stays the reference's dummy
+    std::string bytes;
+    bytes.resize((size_t)n_rows * ((size_t)F + 1) * sizeof(float));
+    float* X = reinterpret_cast<float*>(&bytes[0]);
+    float* y = X + (size_t)n_rows * F;
+    for (uint64_t r = 0; r < n_rows; ++r) {
+        float* xr = X + (size_t)r * F;
+        for (uint32_t c = 0; c < F; ++c) {
+            const uint64_t u = splitmix64(seed ^ ((row0 + r) * (uint64_t)F + c));
+            xr[c] = (float)(u >> 40) * (1.0f / 16777216.0f) * 2.0f - 1.0f;
+        }
+        y[r] = xr[0] > 0.0f ? 1.0f : 0.0f;
+    }
+    more_files_[file_num] = std::move(bytes);
+    return true;
+}
+
+const std::string* FileServerCore::find_file(uint32_t file_num) const {
+    if (file_num == 0) return &file_;
+    auto it = more_files_.find(file_num);
+    return it == more_files_.end() ? nullptr : &it->second;
+}
+
+long long FileServerCore::chunk_of(uint32_t file_num, long long k, const void** data) const {
+    const std::string* f = find_file(file_num);
+    if (!f) return -1;
+    const long long pos = k * kChunkSize;
+    if (k < 0 || pos >= (long long)f->size()) return 0;
+    if (data) *data = f->data() + pos;
+    const long long left = (long long)f->size() - pos;
+    return left < kChunkSize ? left : kChunkSize;
+}
+
 int FileServerCore::DoPush(Directory& dir, const std::string& recipient_addr, uint32_t file_num) {
-    if (file_num != 0) return -1;  // :107-110: the reference prints and calls exit(1)
+    if (!find_file(file_num)) return -1;  // :107-110: the reference prints and calls exit(1)
     WorkerCore* worker = dir.find(recipient_addr);  // :111-113
     if (!worker) return 0;
     bool ok = worker->ReceiveFileBegin();           // WorkerStub::ReceiveFile, :60-87
     for (long long k = 0; ok; ++k) {
         const void* data = nullptr;
-        const long long n = chunk(k, &data);
+        const long long n = chunk_of(file_num, k, &data);
         if (n == 0) break;                          // :69 while (pos < file.length())
         ok = worker->ReceiveFileChunk(data, (size_t)n);  // :72 writer->Write(chunk)
     }
@@ -130,6 +174,14 @@ int MasterCore::RequestPushes(FileServerCore& fs, Directory& dir) {
     int ok = 0;
     for (const std::string& addr : worker_addrs)              // :231-234, sequential, file 0
         if (fs.DoPush(dir, addr, 0) == 1) ++ok;
+    return ok;
+}
+int MasterCore::RequestPushesSharded(FileServerCore& fs, Directory& dir) {
+    const std::vector<std::string> worker_addrs = workers();
+    int ok = 0;
+    uint32_t file_num = 1;
+    for (const std::string& addr : worker_addrs)
+        if (fs.DoPush(dir, addr, file_num++) == 1) ++ok;
     return ok;
 }
 int MasterCore::DoCheckups(FileServerCore& fs, Directory& dir) {
@@ -190,6 +242,20 @@ long long slr_file_server_chunk(slr_file_server* fs, long long k, const void** d
 int slr_file_server_do_push(slr_file_server* fs, slr_directory* d, const char* recipient_addr,
                             unsigned file_num) {
     return fs->core.DoPush(d->dir, recipient_addr, file_num);
+}
+int slr_file_server_add_synthetic_shard(slr_file_server* fs, unsigned file_num, unsigned long long row0,
+                                        unsigned long long n_rows, unsigned F, unsigned long long seed) {
+    return fs->core.AddSyntheticShard(file_num, row0, n_rows, F, seed) ? 1 : 0;
+}
+long long slr_file_server_file_length_of(slr_file_server* fs, unsigned file_num) {
+    const std::string* f = fs->core.find_file(file_num);
+    return f ? (long long)f->size() : -1;
+}
+long long slr_file_server_chunk_of(slr_file_server* fs, unsigned file_num, long long k, const void** data) {
+    return fs->core.chunk_of(file_num, k, data);
+}
+int slr_master_request_pushes_sharded(slr_master* m, slr_file_server* fs, slr_directory* d) {
+    return m->core.RequestPushesSharded(fs->core, d->dir);
 }
 int slr_file_server_check_up(slr_file_server* fs) { return fs->core.CheckUp() ? 1 : 0; }
 

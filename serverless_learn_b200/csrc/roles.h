@@ -75,12 +75,20 @@ class FileServerCore {
     FileServerCore();  // fills file 0, :152-156
     const std::string& file() const { return file_; }
     long long chunk(long long k, const void** data) const;  // :68-76
+    // Beyond the reference: further files, addressed by Push.file_num
+    // (proto:36-39).  File k > 0 is a training shard in the stream layout sl_shard_* expects
+    // (all of X row-major fp32, then the labels): rows [row0, row0+n_rows) of the synthetic
+    // matrix of SURVEY.md §8(d).  Unknown file numbers keep the reference's behaviour.
+    bool AddSyntheticShard(uint32_t file_num, uint64_t row0, uint64_t n_rows, uint32_t F, uint64_t seed);
+    const std::string* find_file(uint32_t file_num) const;
+    long long chunk_of(uint32_t file_num, long long k, const void** data) const;
     // FileServerImpl::DoPush :103-119 -> WorkerStub::ReceiveFile :60-87.  -1: file_num != 0
     int DoPush(Directory& dir, const std::string& recipient_addr, uint32_t file_num);
     bool CheckUp() const { return true; }  // :122-130
 
   private:
     std::string file_;  // :43
+    std::map<uint32_t, std::string> more_files_;
 };
 
 // src/master.cc
@@ -94,6 +102,9 @@ class MasterCore {
     std::vector<std::string> workers();
     bool ExchangeUpdates(const double* delta, int n, double* reply, int n_out);  // :95-114
     int RequestPushes(FileServerCore& fs, Directory& dir);  // one round of :220-237
+    // same round with a shard assignment instead of "file 0 to everyone" (§8f n2): the i-th
+    // registered worker gets file i+1
+    int RequestPushesSharded(FileServerCore& fs, Directory& dir);
     int DoCheckups(FileServerCore& fs, Directory& dir);     // one round of :240-266
 
   private:

@@ -128,24 +128,24 @@ class FileServerService:
     def __init__(self, fs: roles.FileServer):
         self.fs = fs
 
-    def _chunks(self):
+    def _chunks(self, file_num=0):
         k = 0
         while True:
-            ch = self.fs.chunk(k)
+            ch = self.fs.chunk_of(file_num, k)
             if ch.size == 0:
                 return
             yield M["Chunk"](data=ch.tobytes())
             k += 1
 
     def DoPush(self, request, context):                                    # src/file_server.cc:103-119
-        if request.file_num != 0:                                          # reference: exit(1), :107-110
-            context.abort(grpc.StatusCode.INVALID_ARGUMENT, "received push with file_number not 0")
+        if self.fs.file_length_of(request.file_num) < 0:                   # reference: exit(1), :107-110
+            context.abort(grpc.StatusCode.INVALID_ARGUMENT, "received push with unknown file_number")
         with grpc.insecure_channel(request.recipient_addr, options=_CHANNEL_OPTS) as ch:
             call = ch.stream_unary(_method("Worker", "ReceiveFile"),
                                    request_serializer=M["Chunk"].SerializeToString,
                                    response_deserializer=M["ReceiveFileAck"].FromString)
             try:
-                ack = call(self._chunks())
+                ack = call(self._chunks(request.file_num))
                 ok = bool(ack.ok)
             except grpc.RpcError:
                 ok = False

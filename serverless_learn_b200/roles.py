@@ -26,6 +26,11 @@ _SIGS = {
     "slr_file_server_chunk": (C.c_longlong, [_p, C.c_longlong, C.POINTER(_p)]),
     "slr_file_server_do_push": (C.c_int, [_p, _p, C.c_char_p, C.c_uint]),
     "slr_file_server_check_up": (C.c_int, [_p]),
+    "slr_file_server_add_synthetic_shard": (C.c_int, [_p, C.c_uint, C.c_ulonglong, C.c_ulonglong, C.c_uint,
+                                                    C.c_ulonglong]),
+    "slr_file_server_file_length_of": (C.c_longlong, [_p, C.c_uint]),
+    "slr_file_server_chunk_of": (C.c_longlong, [_p, C.c_uint, C.c_longlong, C.POINTER(_p)]),
+    "slr_master_request_pushes_sharded": (C.c_int, [_p, _p, _p]),
     "slr_master_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.POINTER(_p)]),
     "slr_master_destroy": (None, [_p]),
     "slr_master_handle": (_p, [_p]),
@@ -109,6 +114,19 @@ class FileServer:
             return np.zeros(0, np.uint8)
         return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n,))
 
+    def add_synthetic_shard(self, file_num: int, row0: int, n_rows: int, F: int, seed: int = 0x5EED) -> bool:
+        return bool(self.L.slr_file_server_add_synthetic_shard(self.p, file_num, row0, n_rows, F, seed))
+
+    def file_length_of(self, file_num: int) -> int:
+        return int(self.L.slr_file_server_file_length_of(self.p, file_num))
+
+    def chunk_of(self, file_num: int, k: int) -> np.ndarray:
+        ptr = _p()
+        n = self.L.slr_file_server_chunk_of(self.p, file_num, k, C.byref(ptr))
+        if n <= 0:
+            return np.zeros(0, np.uint8)
+        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n,))
+
     def do_push(self, d: Directory, addr: str, file_num: int = 0) -> int:
         return int(self.L.slr_file_server_do_push(self.p, d.p, addr.encode(), file_num))
 
@@ -147,6 +165,9 @@ class Master:
 
     def request_pushes(self, fs: FileServer, d: Directory) -> int:
         return int(self.L.slr_master_request_pushes(self.p, fs.p, d.p))
+
+    def request_pushes_sharded(self, fs: FileServer, d: Directory) -> int:
+        return int(self.L.slr_master_request_pushes_sharded(self.p, fs.p, d.p))
 
     def do_checkups(self, fs: FileServer, d: Directory) -> int:
         return int(self.L.slr_master_do_checkups(self.p, fs.p, d.p))

@@ -99,3 +99,26 @@ def test_worker_trains_on_pushed_synthetic_shard(orc):
     assert np.max(np.abs(w.model() - ref)) / np.max(np.abs(ref)) <= 1e-5
     assert np.max(np.abs(lg - lo) / lo) <= 1e-5
     w.close()
+
+
+def test_sharded_push_then_training(orc):
+    # §8f n2: Push.file_num selects a shard; worker i gets file i+1 through DoPush/ReceiveFile
+    # (1,000,000-byte chunks straddling rows), trains on it, matches the oracle on that shard
+    from serverless_learn_b200 import roles
+    F, B, n = 260, 100, 1500
+    d, fs, master = roles.Directory(), roles.FileServer(), roles.Master(F)
+    ws = [roles.Worker(f"w{k}:1", F, B, eta=0.2) for k in range(2)]
+    for k, w in enumerate(ws):
+        d.add(w)
+        master.register_birth(w.addr)
+        assert fs.add_synthetic_shard(k + 1, k * n, n, F)
+    assert master.request_pushes_sharded(fs, d) == 2
+    for k, w in enumerate(ws):
+        lg = w.train_steps(12)
+        X, y = orc.synth(k * n, n, F)
+        ref = np.zeros(F)
+        lo = orc.lr_steps(X, y, B, 0, 12, ref, 0.2)
+        assert np.max(np.abs(w.model() - ref)) / np.max(np.abs(ref)) <= 1e-5
+        assert np.max(np.abs(lg - lo) / lo) <= 1e-5
+        w.close()
+    master.close(); fs.close(); d.close()

@@ -106,3 +106,19 @@ def test_file_server_file0_and_chunks(libs, orc, file0):
     assert fs.do_push(d, "nobody:1", 1) == -1       # file_num != 0 (reference: exit(1))
     fs.close()
     d.close()
+
+
+def test_file_server_synthetic_shards(libs, orc):
+    from serverless_learn_b200 import roles
+    fs = roles.FileServer()
+    assert not fs.add_synthetic_shard(0, 0, 10, 8)          # file 0 stays the reference's dummy file
+    assert fs.add_synthetic_shard(3, 100, 1000, 260)
+    assert fs.file_length_of(3) == 1000 * 261 * 4 and fs.file_length_of(2) == -1
+    stream = np.concatenate([fs.chunk_of(3, k) for k in range(2)])
+    assert fs.chunk_of(3, 2).size == 0 and stream.size == 1000 * 261 * 4
+    X, y = orc.synth(100, 1000, 260)
+    raw = stream.view(np.float32)
+    assert np.array_equal(raw[:260000].reshape(1000, 260), X) and np.array_equal(raw[260000:], y)
+    d = roles.Directory()
+    assert fs.do_push(d, "nobody:1", 2) == -1 and fs.do_push(d, "nobody:1", 3) == 0
+    fs.close(); d.close()
