@@ -260,6 +260,7 @@ struct LrArgs {
     unsigned xflag0;       // step s of this launch uses packet flag xflag0 + s + 1
     int n_own;             // CTAs that own a slice of the vector in the cross-GPU stage
     int xslice;            // elements per slice (32 in lr_persist_kernel)
+    int rotate_reduce;     // 1: CTA-dependent start line of the bulk reduction
     int hold_refills;      // 1: the producer re-arms slots only after the step's reduction is released
     int direct_total;      // 1: threads read the gradient total straight from L2 instead of a TMA load into smem
     unsigned long long* loss_fix;  // device [n_steps] s64 fixed-point loss sums (zero at launch) or nullptr
@@ -438,8 +439,22 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                 dbg_stamp(a, s, 6);
                 if (XB) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    bulk_reduce_add_u64(buf + (size_t)(c % KREP) * Fp, smem_u32(gout),
-                                        (uint32_t)Fp * 8u);
+                    if (a.rotate_reduce) {
+                        // every CTA of a replica starts its reduction at a different line, so the
+                        // CTAs do not walk the accumulator's lines in lock step
+                        const uint32_t bytes = (uint32_t)Fp * 8u;
+                        const uint32_t lines = bytes / 128u;
+                        const uint32_t per = (uint32_t)(G + KREP - 1) / (uint32_t)KREP;
+                        const uint32_t off = lines ? (((uint32_t)(c / KREP) * lines / per) % lines) * 128u : 0u;
+                        unsigned long long* dst = buf + (size_t)(c % KREP) * Fp;
+                        if (off < bytes)
+                            bulk_reduce_add_u64(reinterpret_cast<unsigned char*>(dst) + off,
+                                                smem_u32(gout) + off, bytes - off);
+                        if (off > 0) bulk_reduce_add_u64(dst, smem_u32(gout), off);
+                    } else {
+                        bulk_reduce_add_u64(buf + (size_t)(c % KREP) * Fp, smem_u32(gout),
+                                            (uint32_t)Fp * 8u);
+                    }
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
                     dbg_stamp(a, s, 7);

@@ -148,7 +148,7 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0;
     unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
     size_t dbg_words = 0;
@@ -425,6 +425,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         CK(h, cudaMemsetAsync(h->counter, 0, 128, h->stream));
         a.eta_over_b = h->eta / (double)h->B;
         a.hold_refills = h->opt_hold != 0 ? 1 : 0;
+        a.rotate_reduce = h->opt_rotate != 0 ? 1 : 0;
         a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && kVariants[plan.variant].kind == 0 && plan.args.krep <= 4) ? 1 : 0;
         if (fused_sync) {
             a.nranks = h->peer_n;
@@ -684,6 +685,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "krep") h->opt_krep = value;
     else if (k == "direct_total") h->opt_direct = value;
     else if (k == "hold_refills") h->opt_hold = value;
+    else if (k == "rotate_reduce") h->opt_rotate = value;
     else if (k == "sync_path") h->opt_sync_path = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;

@@ -122,3 +122,52 @@ def test_sharded_push_then_training(orc):
         assert np.max(np.abs(lg - lo) / lo) <= 1e-5
         w.close()
     master.close(); fs.close(); d.close()
+
+
+def test_async_gossip_training_follows_the_oracle_schedule(orc):
+    # §8f n3: the reference's actual algorithm — every worker trains on its own shard and, at
+    # intervals, exchanges deltas with a rand()%N partner from its CheckUp peer list — run as one
+    # deterministic schedule (R8) on the GPU replicas and in the oracle; also compared with the
+    # synchronous (all-reduce) extension for convergence.
+    from serverless_learn_b200 import roles
+    F, B, n, NW, K, ROUNDS, eta = 64, 32, 640, 4, 5, 6, 0.3
+    d, fs, master = roles.Directory(), roles.FileServer(), roles.Master(F)
+    ws = [roles.Worker(f"w{k}:1", F, B, eta=eta) for k in range(NW)]
+    shards = []
+    for k, w in enumerate(ws):
+        d.add(w)
+        master.register_birth(w.addr)
+        fs.add_synthetic_shard(k + 1, k * n, n, F)
+        shards.append(orc.synth(k * n, n, F))
+    assert master.request_pushes_sharded(fs, d) == NW and master.do_checkups(fs, d) == NW
+    om = [np.zeros(F) for _ in range(NW)]
+    oo = [np.zeros(F) for _ in range(NW)]
+    libc = C.CDLL("libc.so.6")
+    libc.srand(777)
+    draws = [libc.rand() for _ in range(NW * ROUNDS)]
+    libc.srand(777)
+    it = iter(draws)
+    gpu_loss, orc_loss = [], []
+    for rnd in range(ROUNDS):
+        for k, w in enumerate(ws):
+            gpu_loss.append(w.train_steps(K))
+            orc_loss.append(orc.lr_steps(shards[k][0], shards[k][1], B, rnd * K, K, om[k], eta))
+        for k, w in enumerate(ws):
+            j = w.gossip_once(d)
+            assert j == next(it) % NW
+            delta = orc.delta(om[k], oo[k])
+            reply = orc.merge_callee(om[j], oo[j], delta)
+            orc.apply_reply(om[k], oo[k], reply)
+    for k, w in enumerate(ws):
+        err = np.max(np.abs(w.model() - om[k])) / np.max(np.abs(om[k]))
+        assert err <= 1e-5, (k, err)
+    gl, ol = np.concatenate(gpu_loss), np.concatenate(orc_loss)
+    assert np.max(np.abs(gl - ol) / ol) <= 1e-5
+    # convergence: gossip keeps the replicas learning the same rule as synchronous averaging
+    wsync = np.zeros(F)
+    ls = orc.lr_steps_sync([s[0] for s in shards], [s[1] for s in shards], B, 0, K * ROUNDS, wsync, eta)
+    last_async = np.mean([orc_loss[-NW + k][-1] for k in range(NW)])
+    assert last_async < 0.75 * np.log(2) and ls[-1] < 0.75 * np.log(2)
+    for w in ws:
+        w.close()
+    master.close(); fs.close(); d.close()
