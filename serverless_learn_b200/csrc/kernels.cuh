@@ -487,7 +487,6 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                 // NVLink (16-byte data+flag packets), adds the peers' sums as they land, publishes
                 // the all-rank total locally.  s64 adds: exact, identical on every GPU.
                 __syncwarp();  // lane 0 has seen every local CTA's contribution (acquire above)
-                asm volatile("fence.acq_rel.gpu;" ::: "memory");
                 const unsigned xflag = a.xflag0 + (unsigned)s + 1u;
                 const size_t half = (size_t)(xflag & 1u) * (size_t)a.nranks * (size_t)F;
                 unsigned long long* fin = a.fin + (size_t)(s % 3) * F;
@@ -527,7 +526,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                         fin[e] = (unsigned long long)tot;
                     }
                     __syncwarp();
-                    if (lane == 0) red_release_add_u32(a.counter2, 1u);
+                    if (lane == 0) { dbg_stamp(a, s, 7); red_release_add_u32(a.counter2, 1u); }
                 }
                 if (lane == 0) {
                     const unsigned want2 = (unsigned)a.n_own * (unsigned)(s + 1);

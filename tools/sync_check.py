@@ -58,6 +58,26 @@ for mode in ("fused", "nccl"):
     r.shard_synth(BIG, row0=rank * BIG)
     r.train_steps_sync(64, want_loss=False)
     dist.barrier(); torch.cuda.synchronize()
+    if mode == "fused" and os.environ.get("SL_TIMELINE"):
+        import ctypes as C
+        r.set_option("debug_timeline", 100)
+        r.train_steps_sync(256, want_loss=False)
+        G = r.info("grid")
+        buf = np.zeros(4 * G * 16, dtype=np.uint64)
+        assert r._L.sl_debug_read(r._h, buf.ctypes.data_as(C.POINTER(C.c_ulonglong)), buf.size) == 0
+        t = buf.reshape(4, G, 8, 2).astype(np.int64)
+        if rank == 0:
+            names = ["P0 step start", "P1 compute done", "P2 staged", "P3 counter1 bumped", "P4 total load issued",
+                     "P5 weights applied", "P6 owner sent", "P7 owner got peers"]
+            for s_ in (1, 2):
+                g0 = t[s_, :, 0, 1].min()
+                print(f"--- fused step {100 + s_} (rank 0), ns from earliest step start: min/median/max over CTAs")
+                for pnt in (0, 5, 1, 2, 3, 6, 7, 4):
+                    v = t[s_, :, pnt, 1] - g0
+                    v = v[t[s_, :, pnt, 1] > 0]
+                    if v.size:
+                        print(f"  {names[pnt]:24s} {v.min():7d} {int(np.median(v)):7d} {v.max():7d}   (n={v.size})")
+                print(f"  next step start          {int(np.median(t[s_ + 1, :, 0, 1] - g0)):7d}", flush=True)
     r.train_steps_sync(1024, want_loss=True)
     ms = torch.tensor([r.last_train_ms()], device="cuda"); dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     res[mode] = (ew, el, r.info("path"), float(ms.item()) * 1e3 / 1024, r.model())
