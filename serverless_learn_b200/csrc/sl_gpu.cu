@@ -407,8 +407,6 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
     if (want_loss) CK(h, cudaMemsetAsync(h->loss_fix, 0, 8 * (size_t)n_steps, h->stream));
     while (done < n_steps) {
         const int n = std::min(max_per_launch, n_steps - done);
-        // 32-bit flag wrap: equality compare makes wrap harmless, but never emit flag 0
-        // as a "first" flag right after the zero-fill
         slk::LrArgs a = plan.args;
         a.X = reinterpret_cast<const float*>(h->shard);
         a.y = a.X + (size_t)h->n_rows * h->F;

@@ -1,6 +1,7 @@
-"""Multi-GPU parity + timing of sl_train_steps_sync (run under torchrun, one rank per GPU):
+"""(Test infrastructure; lives under tests/ because it uses the oracle.)
+Multi-GPU parity + timing of sl_train_steps_sync (run under torchrun, one rank per GPU):
 the fused peer-memory kernel and the NCCL path against the oracle's W-worker sync loop.
-    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/sync_check.py
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/mgpu_sync_check.py
 """
 import os
 import sys
