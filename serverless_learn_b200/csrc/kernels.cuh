@@ -260,6 +260,7 @@ struct LrArgs {
     unsigned xflag0;       // step s of this launch uses packet flag xflag0 + s + 1
     int n_own;             // CTAs that own a slice of the vector in the cross-GPU stage
     int xslice;            // elements per slice (32 in lr_persist_kernel)
+    int poll_pause;        // SM cycles the exchange thread waits after its bump before it starts polling
     int rotate_reduce;     // 1: CTA-dependent start line of the bulk reduction
     int hold_refills;      // 1: the producer re-arms slots only after the step's reduction is released
     int direct_total;      // 1: threads read the gradient total straight from L2 instead of a TMA load into smem
@@ -465,6 +466,10 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                 dbg_stamp(a, s, 3);
                 const unsigned want = (unsigned)G * (unsigned)(s + 1);
                 uint32_t spins = 0;
+                if (a.poll_pause > 0) {  // the first bumps cannot complete the count: do not poll yet
+                    const long long t0 = clock64();
+                    while (clock64() - t0 < a.poll_pause) {}
+                }
                 while ((int)(ld_relaxed_u32(a.counter) - want) < 0) {
                     if (spin_abort(spins, a.err, kErrTimeoutPart)) break;
                 }

@@ -148,7 +148,8 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0, opt_persist_l2 = 0, opt_poll_pause = 0;
+    bool l2_window_set = false;
     unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
     size_t dbg_words = 0;
@@ -402,6 +403,20 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         const long long cap = ((1ll << 31) - 1 - plan.args.ns) / std::max(1ll, rows_per_cta);
         max_per_launch = (int)std::max(1ll, std::min<long long>(max_per_launch, cap));
     }
+    if (h->opt_persist_l2 && !h->l2_window_set) {
+        // keep the gradient accumulators resident in L2 while 2+ TB/s of rows stream through it
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 4u << 20);
+        cudaStreamAttrValue av;
+        memset(&av, 0, sizeof(av));
+        av.accessPolicyWindow.base_ptr = h->acc;
+        av.accessPolicyWindow.num_bytes = h->acc_bytes;
+        av.accessPolicyWindow.hitRatio = 1.0f;
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        cudaError_t e = cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+        if (e != cudaSuccess) cudaGetLastError();
+        h->l2_window_set = true;
+    }
     int done = 0;
     *h->h_err = 0;
     if (want_loss) CK(h, cudaMemsetAsync(h->loss_fix, 0, 8 * (size_t)n_steps, h->stream));
@@ -424,6 +439,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         a.eta_over_b = h->eta / (double)h->B;
         a.hold_refills = h->opt_hold != 0 ? 1 : 0;
         a.rotate_reduce = h->opt_rotate != 0 ? 1 : 0;
+        a.poll_pause = (int)h->opt_poll_pause;
         a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && kVariants[plan.variant].kind == 0 && plan.args.krep <= 4) ? 1 : 0;
         if (fused_sync) {
             a.nranks = h->peer_n;
@@ -684,6 +700,8 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "direct_total") h->opt_direct = value;
     else if (k == "hold_refills") h->opt_hold = value;
     else if (k == "rotate_reduce") h->opt_rotate = value;
+    else if (k == "persist_l2") h->opt_persist_l2 = value;
+    else if (k == "poll_pause") h->opt_poll_pause = value;
     else if (k == "sync_path") h->opt_sync_path = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
