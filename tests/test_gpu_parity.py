@@ -323,3 +323,33 @@ def test_gossip_p2p_bit_exact(sl, orc, n):
             assert np.array_equal(Bn.model(), bm) and np.array_equal(Bn.old(), bo)
         with pytest.raises(sl.SlError):
             A.gossip_p2p(A)
+
+
+def test_launch_splitting_and_step_reset(sl, orc):
+    n, F, B, steps, eta = 500, 128, 48, 10, 0.2
+    X, y = orc.synth(0, n, F)
+    w = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, steps, w, eta)
+    with sl.Replica(F, B, eta=eta) as r:
+        r.set_option("steps_per_launch", 3)            # 10 steps = 4 cooperative launches
+        r.load_shard(X, y)
+        k0 = r.info("k1_launches")
+        lg = r.train_steps(steps)
+        assert r.info("k1_launches") - k0 == 4 and r.info("step") == steps
+        assert w_err(r.model(), w) <= W_TOL and float(np.max(np.abs(lg - lo) / lo)) <= L_TOL
+        assert r.train_steps(0).size == 0
+        # a new shard restarts the minibatch counter (rows (t*B + j) mod n_rows with t from 0)
+        X2, y2 = orc.synth(7777, n, F)
+        r.load_shard(X2, y2)
+        assert r.info("step") == 0
+        lg2 = r.train_steps(4)
+        lo2 = orc.lr_steps(X2, y2, B, 0, 4, w, eta)
+        assert w_err(r.model(), w) <= W_TOL and float(np.max(np.abs(lg2 - lo2) / lo2)) <= L_TOL
+        # training continues on the sealed shard while the next one streams in
+        r.shard_begin(X.nbytes + y.nbytes)
+        r.shard_append(X)
+        lg3 = r.train_steps(2)                          # still on X2
+        lo3 = orc.lr_steps(X2, y2, B, 4, 2, w, eta)
+        assert float(np.max(np.abs(lg3 - lo3) / lo3)) <= L_TOL
+        r.shard_append(y)
+        assert r.shard_end() == n and r.info("step") == 0
