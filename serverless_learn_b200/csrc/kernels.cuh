@@ -250,7 +250,8 @@ struct LrArgs {
     double* model;         // fp64 master weights [F] (model_state, src/master.cc:58)
     unsigned long long* acc;   // [3][krep][Fp] s64 gradient accumulators (zero at launch)
     unsigned* counter;     // arrivals; zero at launch
-    double* wmaster;       // WS only: [grid][F] per-CTA fp64 master copies
+    double* wmaster;       // WM=1 only: [grid][F] per-CTA fp64 master copies
+    float* w32buf;         // K1w: [2][F] fp32 weights published by the slice owners
     // same-box data parallel (nranks > 1 or peers attached): one kernel per GPU, the kernels
     // talk through peer-mapped memory over NVLink
     int nranks, rank;      // nranks == 0: single-GPU exchange
@@ -260,6 +261,8 @@ struct LrArgs {
     unsigned xflag0;       // step s of this launch uses packet flag xflag0 + s + 1
     int n_own;             // CTAs that own a slice of the vector in the cross-GPU stage
     int xslice;            // elements per slice (32 in lr_persist_kernel)
+    int tma_chunk;         // bytes per bulk copy (a row block is fetched as several copies on one mbarrier)
+    int dbg_skip;          // diagnostics: K1w skips the per-row maths (measures the bare TMA ring rate)
     int poll_pause;        // SM cycles the exchange thread waits after its bump before it starts polling
     int rotate_reduce;     // 1: CTA-dependent start line of the bulk reduction
     int hold_refills;      // 1: the producer re-arms slots only after the step's reduction is released
@@ -416,8 +419,16 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     while (left > 0) {  // one copy unless the rows wrap around the shard end
                         const long long room = a.n_rows - g0;
                         const int n = room < (long long)left ? (int)room : left;
-                        bulk_g2s(dst, a.X + (size_t)g0 * F, (uint32_t)n * (uint32_t)row_bytes, fb,
-                                 pol);
+                        {   // several moderate copies keep more requests in flight than one large one
+                            const unsigned char* srcb = reinterpret_cast<const unsigned char*>(a.X + (size_t)g0 * F);
+                            uint32_t todo = (uint32_t)n * (uint32_t)row_bytes, o = 0;
+                            while (todo > 0) {
+                                const uint32_t m = todo < (uint32_t)a.tma_chunk ? todo : (uint32_t)a.tma_chunk;
+                                bulk_g2s(dst + o, srcb + o, m, fb, pol);
+                                o += m;
+                                todo -= m;
+                            }
+                        }
                         dst += (uint32_t)n * (uint32_t)row_bytes;
                         left -= n;
                         g0 = 0;

@@ -82,7 +82,7 @@ struct Variant {
     Variant { CH, R, RS, NCW, XB, WS, 0, \
               (const void*)slk::lr_persist_kernel<CH, R, RS, NCW, (XB) != 0, WS> }
 #define SL_WIDE(CH, NCW) \
-    Variant { CH, 1, 1, NCW, 1, 1, 1, (const void*)slk::lr_wide_kernel<CH, NCW> }
+    Variant { CH, 1, 1, NCW, 1, 0, 1, (const void*)slk::lr_wide_kernel<CH, NCW> }
 const Variant kVariants[] = {
     SL_VARIANT(1, 16, 4, 8, 1, 0),    // 1: F <= 1024; measured best at F=1024, B/grid = 28
     SL_VARIANT(1, 16, 4, 16, 1, 0),   // 2: F <= 2048; two row groups of 16 rows
@@ -94,7 +94,7 @@ const Variant kVariants[] = {
     SL_VARIANT(8, 1, 1, 16, 0, 1),    // 8: F <= 16384, weights in shared memory
     SL_VARIANT(8, 2, 1, 8, 0, 1),     // 9: F <= 8192,  weights in shared memory
     SL_VARIANT(4, 4, 4, 14, 1, 2),    // 10: F <= 1024 as 7 row groups of 2 warps x 4 rows: 28 rows in one pass
-    SL_WIDE(10, 14),                  // 11: F <= 17920, wide-row kernel, 14+2 warps = 128 registers/thread
+    SL_WIDE(10, 14),                  // 11: F <= 17920, wide-row kernel, 14+1 warps = 128 registers/thread
     SL_WIDE(5, 14),                   // 12: F <= 8960,  wide-row kernel
     SL_WIDE(2, 16),                   // 13: F <= 4096,  wide-row kernel
 };
@@ -137,7 +137,8 @@ struct sl_handle {
     unsigned long long* acc = nullptr;   // [3][krep][Fp] gradient accumulators
     size_t acc_bytes = 0;
     unsigned* counter = nullptr;
-    double* wmaster = nullptr;           // [grid][F] (wide-row variants)
+    double* wmaster = nullptr;           // [grid][F] (WM=1 variants)
+    float* w32buf = nullptr;             // [2][F] (K1w)
     size_t wmaster_bytes = 0;
     double* d_loss = nullptr;
     double* h_loss = nullptr;
@@ -148,7 +149,7 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0, opt_persist_l2 = 0, opt_poll_pause = 0;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0, opt_persist_l2 = 0, opt_poll_pause = 0, opt_dbg_skip = 0, opt_tma_chunk = 0;
     bool l2_window_set = false;
     unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
@@ -305,10 +306,10 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
         a.krep = 1;
         a.row_bytes = 4 * F;
         a.zy_rows = (h->B + grid - 1) / grid;
-        a.xslice = 32 * ((F + 32 * grid - 1) / (32 * grid));
+        a.xslice = 4 * ((F + 4 * grid - 1) / (4 * grid));  // columns a slice owner sums and updates
         const size_t red_w = sizeof(float) * 2 * v.ncw;
         const size_t zy_w = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
-        const size_t gout_w = 8 * (size_t)v.ncw * 32 * 4;
+        const size_t gout_w = 8 * (size_t)v.ncw * 32 * 2 + 64;  // owner partial sums: groups x slice
         const size_t fixed_w = red_w + zy_w + gout_w + 512;
         if (h->smem_optin < fixed_w + 16 + (size_t)a.row_bytes) { *why = "row does not fit in shared memory"; return false; }
         size_t nsw = (h->smem_optin - fixed_w) / ((size_t)a.row_bytes + 16);
@@ -365,7 +366,8 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
 
 int ensure_exchange(sl_handle* h, const PersistPlan& plan) {
     const Variant& v = kVariants[plan.variant];
-    const size_t need = 8 * (size_t)3 * plan.args.krep * plan.args.Fp;
+    const size_t need = v.kind == 1 ? 8 * (size_t)plan.grid * plan.args.Fp   // K1w: one partial vector per CTA
+                                    : 8 * (size_t)3 * plan.args.krep * plan.args.Fp;
     if (h->acc_bytes < need) {
         if (h->acc) cudaFree(h->acc);
         h->acc = nullptr;
@@ -374,6 +376,7 @@ int ensure_exchange(sl_handle* h, const PersistPlan& plan) {
         h->acc_bytes = need;
     }
     if (!h->counter) CK(h, cudaMalloc(&h->counter, 256));
+    if (v.kind == 1 && !h->w32buf) CK(h, cudaMalloc(&h->w32buf, sizeof(float) * 2 * (size_t)h->F));
     if (v.ws == 1) {
         const size_t wb = sizeof(double) * (size_t)plan.grid * h->F;
         if (h->wmaster_bytes < wb) {
@@ -394,7 +397,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
     if (rc) return rc;
     CK(h, cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
     int occ = 0;
-    CK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, (v.ncw + 2) * 32, plan.smem));
+    CK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, (v.ncw + 2 - v.kind) * 32, plan.smem));
     if (occ < 1) return fail(h, SL_ECUDA, "persistent kernel does not fit on an SM");
     int max_per_launch =
         h->opt_steps_per_launch > 0 ? (int)h->opt_steps_per_launch : kMaxStepsPerLaunch;
@@ -432,14 +435,22 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         a.acc = h->acc;
         a.counter = h->counter;
         a.wmaster = h->wmaster;
+        a.w32buf = h->w32buf;
+        if (kVariants[plan.variant].kind == 1) {  // the wide kernel always runs its owner stage
+            a.counter2 = h->counter + 16;
+            a.n_own = (h->F + plan.args.xslice - 1) / plan.args.xslice;
+        }
         a.loss_fix = want_loss ? h->loss_fix + done : nullptr;
         // accumulators and the arrival counter start every launch at zero
-        CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
+        if (kVariants[plan.variant].kind == 0)
+            CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 128, h->stream));
         a.eta_over_b = h->eta / (double)h->B;
         a.hold_refills = h->opt_hold != 0 ? 1 : 0;
         a.rotate_reduce = h->opt_rotate != 0 ? 1 : 0;
         a.poll_pause = (int)h->opt_poll_pause;
+        a.dbg_skip = h->opt_dbg_skip != 0 ? 1 : 0;
+        a.tma_chunk = h->opt_tma_chunk > 0 ? (int)((h->opt_tma_chunk + 15) / 16 * 16) : (1 << 20);
         a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && kVariants[plan.variant].kind == 0 && plan.args.krep <= 4) ? 1 : 0;
         if (fused_sync) {
             a.nranks = h->peer_n;
@@ -468,7 +479,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
             a.dbg_step = (int)h->opt_dbg_step;
         }
         void* params[] = {&a};
-        CK(h, cudaLaunchCooperativeKernel(v.fn, dim3(plan.grid), dim3((v.ncw + 2) * 32), params,
+        CK(h, cudaLaunchCooperativeKernel(v.fn, dim3(plan.grid), dim3((v.ncw + 2 - v.kind) * 32), params,
                                           plan.smem, h->stream));
         h->launches++;
         h->k1_launches++;
@@ -660,7 +671,7 @@ int sl_destroy(sl_handle* h) {
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->model); cudaFree(h->old); cudaFree(h->shard); cudaFree(h->in_buf);
-    cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->d_loss); cudaFree(h->loss_fix);
+    cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->w32buf); cudaFree(h->d_loss); cudaFree(h->loss_fix);
     cudaFree(h->dbg);
     for (int p = 0; p < h->peer_n; ++p)
         if (p != h->peer_rank && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
@@ -702,6 +713,8 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "rotate_reduce") h->opt_rotate = value;
     else if (k == "persist_l2") h->opt_persist_l2 = value;
     else if (k == "poll_pause") h->opt_poll_pause = value;
+    else if (k == "debug_skip_compute") h->opt_dbg_skip = value;
+    else if (k == "tma_chunk") h->opt_tma_chunk = value;
     else if (k == "sync_path") h->opt_sync_path = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
