@@ -379,8 +379,8 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         }
         {   // arrivals that complete "gradient staged": the warps (XB) or threads that write it
             const int granules = F / 4;
-            const int comb_warps = RG > 1 ? (granules + 31) / 32 : WPG;
-            const int comb_threads = RG > 1 ? granules : WPG * 32;
+            const int comb_warps = RG > 1 ? min(NCW, (granules + 31) / 32) : WPG;
+            const int comb_threads = RG > 1 ? min(granules, NCW * 32) : WPG * 32;
             mbar_init(smem_u32(gfull), XB ? comb_warps : comb_threads);
         }
         mbar_init(smem_u32(wfull), 1);
@@ -849,8 +849,8 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                 int gqc;
                 float4 t;
                 if (RG > 1) {
-                    if (ch > 0) break;
-                    gqc = tid;
+                    gqc = tid + ch * NCT;  // CH*NCT >= granules: every column chunk has a thread
+                    if (gqc >= granules) break;
                     t = *reinterpret_cast<const float4*>(gsm + gqc * 4);
                     for (int k = 1; k < RG; ++k) {
                         const float4 o = *reinterpret_cast<const float4*>(gsm + (size_t)k * F + gqc * 4);
@@ -880,7 +880,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         if (XB) {
             // one arrival per warp that holds staging threads; the warp-wide sync sits outside
             // the (possibly divergent) staging branch
-            const int comb_warps = RG > 1 ? (granules + 31) / 32 : WPG;
+            const int comb_warps = RG > 1 ? min(NCW, (granules + 31) / 32) : WPG;
             __syncwarp();
             if (lane == 0 && warp < comb_warps) mbar_arrive(smem_u32(gfull));
         }

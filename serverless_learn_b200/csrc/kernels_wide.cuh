@@ -27,12 +27,14 @@ __device__ __forceinline__ longlong2 ld_vol_s64x2(const long long* p) {
     return v;
 }
 
-template <int CH, int NCW>
+template <int CH, int NCW, int NG>
 __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int c = blockIdx.x, G = gridDim.x;
     constexpr int NCT = NCW * 32;
+    constexpr int GW = NCW / NG, GT = GW * 32;  // NG row groups of GW warps: a group works on one row
+    static_assert(GW * NG == NCW, "row groups must divide the compute warps");
 
     unsigned char* ring = smem;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.off_bar);   // [ns]
@@ -57,7 +59,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     if (tid == 0) {
         for (int s = 0; s < ns; ++s) {
             mbar_init(smem_u32(&full[s]), 1);
-            mbar_init(smem_u32(&empty[s]), NCW);
+            mbar_init(smem_u32(&empty[s]), GW);
         }
         fence_mbar_init();
     }
@@ -93,10 +95,11 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     }
 
     // =========================================================================== compute
-    const int ct = warp * 32 + lane;
-    // column chunk ch of this thread: float4 index ct + ch*NCT (valid while it is inside the row)
-#define GQ(ch) (ct + (ch) * NCT)
-#define GV(ch) ((ct + (ch) * NCT) * 4 < F)
+    const int grp = warp / GW;                  // my row group: rows grp, grp+NG, ... of the CTA's rows
+    const int ct = (warp % GW) * 32 + lane;     // my index inside the group
+    // column chunk ch of this thread: float4 index ct + ch*GT (valid while it is inside the row)
+#define GQ(ch) (ct + (ch) * GT)
+#define GV(ch) ((ct + (ch) * GT) * 4 < F)
     float4 w[CH];
 #pragma unroll
     for (int ch = 0; ch < CH; ++ch) {
@@ -134,7 +137,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     // owner stage geometry: this CTA owns columns [c*L, c*L+L); a thread adds the partials
     // p = grp, grp+ngrp, ... of one pair of columns
     const int L = a.xslice, pairs = L >> 1;
-    const int ngrp = max(1, min(NCT / pairs, G));
+    const int P = G * NG;                                // partial vectors: one per row group
+    const int ngrp = max(1, min(NCT / pairs, P));
     const int oj = tid % pairs, ogrp = tid / pairs;
     const int oe = c * L + 2 * oj;                       // first column of my pair
     const bool osum = c < a.n_own && ogrp < ngrp && oe < F;
@@ -142,10 +146,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     const bool oupd = c < a.n_own && tid < L && ue < F;
     long long* part = reinterpret_cast<long long*>(a.acc);
 
-    uint32_t slot = 0, par = 0;
     int red_buf = 0;
+    uint32_t slot = 0, par = 0;
     long long mb = mb0;
-    float y_next = (nrows_c > 0 && lane == 0) ? __ldg(a.y + (size_t)wrap(mb + lo)) : 0.f;
+    float y_next = (grp < nrows_c && lane == 0) ? __ldg(a.y + (size_t)wrap(mb + lo + grp)) : 0.f;
 
     for (int s = 0; s < a.n_steps; ++s) {
         const long long mb_next = wrap(mb + a.B);
@@ -159,17 +163,31 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
             apply_total(s - 1);
             if (tid == 0) dbg_stamp(a, s, 5);
         }
-        for (int i = 0; i < nrows_c; ++i) {
+        // ring position of my group's first row of this step (the producer fills slots in row order)
+        if constexpr (NG > 1) {
+            const uint32_t q0 = (uint32_t)s * (uint32_t)nrows_c + (uint32_t)grp;
+            slot = q0 % (uint32_t)ns;
+            par = (q0 / (uint32_t)ns) & 1u;
+        }
+        auto next_slot = [&]() {
+            if constexpr (NG == 1) {
+                if (++slot == (uint32_t)ns) { slot = 0; par ^= 1u; }
+            } else {
+                slot += NG;
+                while (slot >= (uint32_t)ns) { slot -= (uint32_t)ns; par ^= 1u; }
+            }
+        };
+        for (int i = grp; i < nrows_c; i += NG) {
             const float yv = __shfl_sync(0xffffffffu, y_next, 0);
-            if (lane == 0) {  // label of the next row (maybe the next step's first)
-                if (i + 1 < nrows_c) y_next = __ldg(a.y + (size_t)wrap(mb + lo + i + 1));
-                else if (s + 1 < a.n_steps) y_next = __ldg(a.y + (size_t)wrap(mb_next + lo));
+            if (lane == 0) {  // label of my group's next row (maybe the next step's first)
+                if (i + NG < nrows_c) y_next = __ldg(a.y + (size_t)wrap(mb + lo + i + NG));
+                else if (s + 1 < a.n_steps && grp < nrows_c) y_next = __ldg(a.y + (size_t)wrap(mb_next + lo + grp));
             }
             mbar_wait(smem_u32(&full[slot]), par, a.err);
             if (a.dbg_skip) {  // diagnostics only: consume the slot without touching it
                 __syncwarp();
                 if (lane == 0) mbar_arrive(smem_u32(&empty[slot]));
-                if (++slot == (uint32_t)ns) { slot = 0; par ^= 1u; }
+                next_slot();
                 continue;
             }
             const uint32_t rb = smem_u32(ring + (size_t)slot * row_bytes);
@@ -185,15 +203,15 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                 }
             }
             acc = warp_sum(acc);
-            float* rbuf = red + red_buf * NCW;
-            if (lane == 0) rbuf[warp] = acc;
-            named_bar_sync(1, NCT);
+            float* rbuf = red + red_buf * NCW + grp * GW;
+            if (lane == 0) rbuf[warp % GW] = acc;
+            named_bar_sync(2 + grp, GT);
             float z = 0.f;
 #pragma unroll
-            for (int k = 0; k < NCW; ++k) z += rbuf[k];
+            for (int k = 0; k < GW; ++k) z += rbuf[k];
             red_buf ^= 1;
             const float resid = sigmoid_f(z) - yv;
-            if (tid == 0 && a.loss_fix) zyb[i] = make_float2(z, yv);
+            if (ct == 0 && a.loss_fix) zyb[i] = make_float2(z, yv);
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch) {
                 if (GV(ch)) {
@@ -206,14 +224,14 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(&empty[slot]));
-            if (++slot == (uint32_t)ns) { slot = 0; par ^= 1u; }
+            next_slot();
         }
         if (tid == 0) dbg_stamp(a, s, 1);
-        // ---- phase 1: this CTA's partial gradient, fixed point, straight from registers to L2 ----
+        // ---- phase 1: this row group's partial gradient, fixed point, straight from registers to L2 ----
         // (one buffer is enough: it is rewritten only after the weights of this step arrived,
         // i.e. after every owner finished reading it)
         {
-            long long* mine = part + (size_t)c * a.Fp;
+            long long* mine = part + (size_t)(c * NG + grp) * a.Fp;
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch) {
                 if (GV(ch)) {
@@ -245,7 +263,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                 long long t0 = 0, t1 = 0, u0 = 0, u1 = 0;
                 const long long* src = part + oe;
                 int pp = ogrp;
-                for (; pp + 3 * ngrp < G; pp += 4 * ngrp) {
+                for (; pp + 3 * ngrp < P; pp += 4 * ngrp) {
                     const longlong2 v0 = ld_vol_s64x2(src + (size_t)pp * a.Fp);
                     const longlong2 v1 = ld_vol_s64x2(src + (size_t)(pp + ngrp) * a.Fp);
                     const longlong2 v2 = ld_vol_s64x2(src + (size_t)(pp + 2 * ngrp) * a.Fp);
@@ -253,7 +271,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                     t0 += v0.x + v2.x; t1 += v0.y + v2.y;
                     u0 += v1.x + v3.x; u1 += v1.y + v3.y;
                 }
-                for (; pp < G; pp += ngrp) {
+                for (; pp < P; pp += ngrp) {
                     const longlong2 v0 = ld_vol_s64x2(src + (size_t)pp * a.Fp);
                     t0 += v0.x; t1 += v0.y;
                 }

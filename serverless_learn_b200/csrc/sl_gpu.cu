@@ -81,8 +81,9 @@ struct Variant {
 #define SL_VARIANT(CH, R, RS, NCW, XB, WS) \
     Variant { CH, R, RS, NCW, XB, WS, 0, \
               (const void*)slk::lr_persist_kernel<CH, R, RS, NCW, (XB) != 0, WS> }
-#define SL_WIDE(CH, NCW) \
-    Variant { CH, 1, 1, NCW, 1, 0, 1, (const void*)slk::lr_wide_kernel<CH, NCW> }
+// wide-row kernel: `r` holds the number of row groups
+#define SL_WIDE(CH, NCW, NG) \
+    Variant { CH, NG, 1, NCW, 1, 0, 1, (const void*)slk::lr_wide_kernel<CH, NCW, NG> }
 const Variant kVariants[] = {
     SL_VARIANT(1, 16, 4, 8, 1, 0),    // 1: F <= 1024; measured best at F=1024, B/grid = 28
     SL_VARIANT(1, 16, 4, 16, 1, 0),   // 2: F <= 2048; two row groups of 16 rows
@@ -94,12 +95,18 @@ const Variant kVariants[] = {
     SL_VARIANT(8, 1, 1, 16, 0, 1),    // 8: F <= 16384, weights in shared memory
     SL_VARIANT(8, 2, 1, 8, 0, 1),     // 9: F <= 8192,  weights in shared memory
     SL_VARIANT(4, 4, 4, 14, 1, 2),    // 10: F <= 1024 as 7 row groups of 2 warps x 4 rows: 28 rows in one pass
-    SL_WIDE(10, 14),                  // 11: F <= 17920, wide-row kernel, 14+1 warps = 128 registers/thread
-    SL_WIDE(5, 14),                   // 12: F <= 8960,  wide-row kernel
-    SL_WIDE(2, 16),                   // 13: F <= 4096,  wide-row kernel
+    SL_WIDE(10, 14, 1),               // 11: F <= 17920, wide-row kernel, 14+1 warps = 128 registers/thread
+    SL_WIDE(5, 14, 1),                // 12: F <= 8960,  wide-row kernel
+    SL_WIDE(2, 16, 1),                // 13: F <= 4096,  wide-row kernel
+    SL_WIDE(10, 14, 2),               // 14: F <= 8960,  two row groups of 7 warps
+    SL_WIDE(5, 14, 2),                // 15: F <= 4480,  two row groups of 7 warps
+    SL_WIDE(4, 16, 2),                // 16: F <= 4096,  two row groups of 8 warps
+    SL_WIDE(4, 16, 4),                // 17: F <= 2048,  four row groups of 4 warps
+    SL_WIDE(8, 12, 4),                // 18: F <= 3072,  four row groups of 3 warps
+    SL_WIDE(2, 16, 4),                // 19: F <= 1024,  four row groups of 4 warps
 };
 // auto-selection: the first of these that is wide enough for F
-const int kAutoOrder[] = {1, 2, 6, 12, 11};
+const int kAutoOrder[] = {1, 5, 15, 14, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 }  // namespace
@@ -270,6 +277,9 @@ struct PersistPlan {
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// float4 columns a variant can hold in registers (the wide kernel splits its warps into row groups)
+int variant_granules(const Variant& v) { return v.ch * 32 * (v.kind == 1 ? v.ncw / v.r : v.ncw); }
+
 // Returns false (with reason) when the persistent kernel cannot run this shape.
 bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     const int F = h->F;
@@ -280,14 +290,14 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     int vi = -1;
     if (h->opt_variant > 0 && h->opt_variant <= kNumVariants) {
         vi = (int)h->opt_variant - 1;
-        if (granules > kVariants[vi].ch * 32 * kVariants[vi].ncw) {
+        if (granules > variant_granules(kVariants[vi])) {
             *why = "requested variant too narrow for F";
             return false;
         }
     } else {
         for (int k : kAutoOrder) {
             const int i = k - 1;
-            if (granules <= kVariants[i].ch * 32 * kVariants[i].ncw) { vi = i; break; }
+            if (granules <= variant_granules(kVariants[i])) { vi = i; break; }
         }
         if (vi < 0) { *why = "F too wide for the persistent kernel"; return false; }
     }
@@ -366,7 +376,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
 
 int ensure_exchange(sl_handle* h, const PersistPlan& plan) {
     const Variant& v = kVariants[plan.variant];
-    const size_t need = v.kind == 1 ? 8 * (size_t)plan.grid * plan.args.Fp   // K1w: one partial vector per CTA
+    const size_t need = v.kind == 1 ? 8 * (size_t)plan.grid * v.r * plan.args.Fp   // K1w: one partial vector per row group
                                     : 8 * (size_t)3 * plan.args.krep * plan.args.Fp;
     if (h->acc_bytes < need) {
         if (h->acc) cudaFree(h->acc);
