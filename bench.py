@@ -310,8 +310,39 @@ def run_b200(args, rank, world, local_rank):
     barrier()
     del big
 
+    # ---- extra: config 5's shape (wide rows, F = B = 16384) on the same box, device-resident ----
+    # not the headline workload: one more line of evidence for the wide-row kernel (K1w)
+    wide = None
+    try:
+        WF, WB, wrows, wsteps = 16384, 16384, 1 << 17, 64
+        rw = Replica(WF, WB, eta=ETA, device=local_rank)
+        rw.shard_synth(wrows, row0=rank * wrows)
+        if multi:
+            uid3 = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                uid3.copy_(torch.frombuffer(bytearray(Replica.comm_unique_id()), dtype=torch.uint8))
+            dist.broadcast(uid3, 0)
+            rw.comm_init_rank(world, rank, bytes(uid3.cpu().numpy().tobytes()))
+            attach_peers(rw)
+        wstep = rw.train_steps_sync if multi else rw.train_steps
+        wstep(8, want_loss=True)
+        barrier()
+        wstep(wsteps, want_loss=True)
+        torch.cuda.synchronize()
+        w_s = max_over_ranks(rw.last_train_ms() * 1e-3)
+        barrier()
+        wide = {"workload": f"config 5 shape: F={WF}, B={WB} per GPU, {wrows} rows resident per GPU (8 GiB > L2)",
+                "value": world * wsteps * WB / w_s, "unit": UNIT, "ms_per_step": 1e3 * w_s / wsteps,
+                "steps": wsteps, "variant": rw.info("variant"),
+                "hbm_gbs_per_gpu": algorithmic_bytes_per_step(WF, WB) * wsteps / w_s / 1e9}
+        rw.close()
+    except Exception as ex:  # the headline line must not depend on this extra
+        wide = {"error": repr(ex)}
+
     if rank == 0:
         peak, peak_src = measured_peak()
+        if wide and "hbm_gbs_per_gpu" in wide:
+            wide["roofline_frac"] = wide["hbm_gbs_per_gpu"] / peak
         algo = algorithmic_bytes_per_step() * args.steps / k1
         per_launch_s = dev_ms * 1e-3 / k1
         achieved = algo / per_launch_s / 1e9
@@ -346,6 +377,7 @@ def run_b200(args, rank, world, local_rank):
                                      "back, all timed", "h2d_bytes": res_bytes, "d2h_bytes": 8 * res_steps},
             "gpu_launches": int(launches),
             "clocks": sampler.result(),
+            "config5_shape": wide,
         }
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_port()
