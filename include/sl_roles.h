@@ -73,6 +73,24 @@ int slr_master_request_pushes(slr_master* m, slr_file_server* fs, slr_directory*
 int slr_master_request_pushes_sharded(slr_master* m, slr_file_server* fs, slr_directory* d);
 /* one round of periodically_do_checkups (:240-266): every worker receives the full peer list */
 int slr_master_do_checkups(slr_master* m, slr_file_server* fs, slr_directory* d);
+/* Beyond the reference — elastic membership; off unless enabled, the calls
+ * above keep the reference's behaviour (append-only list src/master.cc:84-85, failed check-ups
+ * ignored src/master.cc:190-195, no model for a late joiner).
+ *  enable_elastic : a worker that fails `max_missed` check-up rounds in a row is dropped and its
+ *                   shard number freed.
+ *  admit_pending  : every worker not admitted yet gets the lowest free shard (file_num >= 1,
+ *                   pushed once, src/file_server.cc:103-119 path) and the master's current model
+ *                   through Worker.ExchangeUpdates (src/worker.cc:81-100) with delta = model/lambda,
+ *                   reply ignored.  Returns the number admitted (< 0: not enabled / error).
+ *  gossip_once    : the master-side initiator the reference holds as dead code
+ *                   (periodically_send_updates, src/master.cc:268-293), one round.
+ *  shard_of       : shard number the master assigned to addr (0: none).
+ *  slr_directory_remove : the worker's server is gone; calls to addr fail from now on. */
+int slr_master_enable_elastic(slr_master* m, int max_missed);
+int slr_master_admit_pending(slr_master* m, slr_file_server* fs, slr_directory* d);
+int slr_master_gossip_once(slr_master* m, slr_directory* d);
+int slr_master_shard_of(slr_master* m, const char* addr);
+int slr_directory_remove(slr_directory* d, const char* addr);
 
 /* ---- worker (src/worker.cc) --------------------------------------------------------------- */
 int slr_worker_create(int device, const char* addr, int D, int F, int B, double eta, double lambda,

@@ -152,7 +152,7 @@ int FileServerCore::DoPush(Directory& dir, const std::string& recipient_addr, ui
 }
 
 // ------------------------------------------------------------------------------------ master
-MasterCore::MasterCore(int device, int D, int B, double eta, double lambda) : D_(D) {
+MasterCore::MasterCore(int device, int D, int B, double eta, double lambda) : D_(D), lambda_(lambda) {
     if (sl_create(device, D, D, B, eta, lambda, &h_) != 0) h_ = nullptr;
 }
 MasterCore::~MasterCore() { sl_destroy(h_); }
@@ -188,13 +188,89 @@ int MasterCore::DoCheckups(FileServerCore& fs, Directory& dir) {
     fs.CheckUp();                                             // :247
     const std::vector<std::string> worker_addrs = workers();  // :249-254
     int reached = 0;
+    std::vector<std::string> lost;
     for (const std::string& addr : worker_addrs) {            // :256-262
         WorkerCore* w = dir.find(addr);
-        if (!w) continue;                                     // "checkup failed", ignored (:190-195)
+        if (!w) {                                             // "checkup failed", ignored (:190-195)
+            if (elastic_) {
+                std::lock_guard<std::mutex> lk(workers_mutex_);
+                if (++members_[addr].missed >= max_missed_) lost.push_back(addr);
+            }
+            continue;
+        }
+        if (elastic_) {
+            std::lock_guard<std::mutex> lk(workers_mutex_);
+            members_[addr].missed = 0;
+        }
         w->CheckUp(worker_addrs);  // WorkerStub::CheckUp sends the full list, self included (:184-188)
         ++reached;
     }
+    if (!lost.empty()) {  // n4: drop workers that stayed silent; survivors learn it at the next round
+        std::lock_guard<std::mutex> lk(workers_mutex_);
+        for (const std::string& addr : lost) {
+            for (size_t i = 0; i < workers_.size();)
+                if (workers_[i] == addr) workers_.erase(workers_.begin() + (long)i); else ++i;
+            members_.erase(addr);
+        }
+    }
     return reached;
+}
+
+int MasterCore::ShardOf(const std::string& addr) {
+    std::lock_guard<std::mutex> lk(workers_mutex_);
+    auto it = members_.find(addr);
+    return it == members_.end() ? 0 : (int)it->second.shard;
+}
+
+int MasterCore::AdmitPending(FileServerCore& fs, Directory& dir) {
+    if (!elastic_) return -1;
+    const double lambda = lambda_;
+    if (lambda == 0.0) return -2;
+    int admitted = 0;
+    for (const std::string& addr : workers()) {
+        uint32_t shard = 0;
+        {
+            std::lock_guard<std::mutex> lk(workers_mutex_);
+            Member& m = members_[addr];
+            if (m.admitted) continue;
+            if (m.shard == 0) {  // lowest shard number nobody holds
+                for (uint32_t cand = 1; m.shard == 0; ++cand) {
+                    bool taken = false;
+                    for (const auto& kv : members_) taken = taken || kv.second.shard == cand;
+                    if (!taken) m.shard = cand;
+                }
+            }
+            shard = m.shard;
+        }
+        WorkerCore* w = dir.find(addr);
+        if (!w) continue;                                  // not reachable yet: stays pending
+        if (fs.DoPush(dir, addr, shard) != 1) continue;    // unknown file / failed push: stays pending
+        // the current model, through the worker's ExchangeUpdates handler
+        std::vector<double> seed((size_t)D_), ignored((size_t)D_);
+        if (sl_get_model(h_, seed.data(), D_) != 0) return -2;
+        for (double& v : seed) v /= lambda;
+        if (!w->ExchangeUpdates(seed.data(), D_, ignored.data(), D_)) continue;
+        {
+            std::lock_guard<std::mutex> lk(workers_mutex_);
+            members_[addr].admitted = true;
+        }
+        ++admitted;
+    }
+    return admitted;
+}
+
+int MasterCore::GossipOnce(Directory& dir) {
+    // periodically_send_updates, src/master.cc:268-293 (never started by the reference's main)
+    const std::vector<std::string> worker_addrs = workers();
+    if (worker_addrs.empty()) return -1;
+    const int lucky_worker_index = rand() % (int)worker_addrs.size();  // :274
+    WorkerCore* w = dir.find(worker_addrs[(size_t)lucky_worker_index]);
+    if (!w) return -1;
+    std::vector<double> update((size_t)D_), update_back((size_t)D_);
+    if (sl_delta_snapshot(h_, update.data(), D_) != 0) return -2;      // :279-282
+    if (!w->ExchangeUpdates(update.data(), D_, update_back.data(), D_)) return -1;
+    if (sl_apply_reply(h_, update_back.data(), D_) != 0) return -2;    // :289 old = model
+    return lucky_worker_index;
 }
 
 }  // namespace slr
@@ -294,6 +370,21 @@ int slr_master_exchange_updates_wire(slr_master* m, const void* in, long in_len,
 int slr_master_request_pushes(slr_master* m, slr_file_server* fs, slr_directory* d) {
     return m->core.RequestPushes(fs->core, d->dir);
 }
+int slr_directory_remove(slr_directory* d, const char* addr) {
+    if (!d || !addr) return 0;
+    d->dir.remove(addr);
+    return 1;
+}
+int slr_master_enable_elastic(slr_master* m, int max_missed) {
+    if (!m) return 0;
+    m->core.EnableElastic(max_missed);
+    return 1;
+}
+int slr_master_admit_pending(slr_master* m, slr_file_server* fs, slr_directory* d) {
+    return m->core.AdmitPending(fs->core, d->dir);
+}
+int slr_master_gossip_once(slr_master* m, slr_directory* d) { return m->core.GossipOnce(d->dir); }
+int slr_master_shard_of(slr_master* m, const char* addr) { return addr ? m->core.ShardOf(addr) : 0; }
 int slr_master_do_checkups(slr_master* m, slr_file_server* fs, slr_directory* d) {
     return m->core.DoCheckups(fs->core, d->dir);
 }

@@ -29,6 +29,10 @@ class Directory {
         auto it = map_.find(addr);
         return it == map_.end() ? nullptr : it->second;
     }
+    void remove(const std::string& addr) {  // the worker's server went away: calls to it fail from now on
+        std::lock_guard<std::mutex> lk(mu_);
+        map_.erase(addr);
+    }
 
   private:
     std::mutex mu_;
@@ -107,11 +111,32 @@ class MasterCore {
     int RequestPushesSharded(FileServerCore& fs, Directory& dir);
     int DoCheckups(FileServerCore& fs, Directory& dir);     // one round of :240-266
 
+    // ---- beyond the reference: elastic membership, off unless enabled ----
+    // The reference never removes a worker (:84-85 only appends), pushes file 0 to everybody every
+    // 5 s (:231-235) and gives a late joiner no model.  With `EnableElastic(k)`:
+    //  * a worker that fails k check-ups in a row is dropped from the list (and from the peer lists
+    //    the next check-up sends); its shard number returns to the free pool;
+    //  * `AdmitPending` gives every not-yet-admitted worker the lowest free shard (file_num >= 1,
+    //    pushed once through the file server) and the master's current model — over the existing
+    //    wire surface: one Worker.ExchangeUpdates with delta = model/lambda, reply ignored, which
+    //    leaves the joiner with model = old = the master's model (exact when lambda is a power of 2);
+    //  * `GossipOnce` is the master-side initiator the reference has as dead code
+    //    (periodically_send_updates, :268-293), so that the master's model follows the workers'.
+    void EnableElastic(int max_missed) { elastic_ = true; max_missed_ = max_missed < 1 ? 1 : max_missed; }
+    int AdmitPending(FileServerCore& fs, Directory& dir);  // returns the number admitted, <0: error
+    int GossipOnce(Directory& dir);                         // partner index, -1 none/unreachable, -2 error
+    int ShardOf(const std::string& addr);                   // 0 = none
+
   private:
+    struct Member { uint32_t shard = 0; bool admitted = false; int missed = 0; };
     sl_handle* h_ = nullptr;
     int D_;
     std::vector<std::string> workers_;  // :63 (WorkerInfo holds only the address, :49-56)
     std::mutex workers_mutex_;          // :66
+    double lambda_ = 0.5;
+    bool elastic_ = false;
+    int max_missed_ = 3;
+    std::map<std::string, Member> members_;  // guarded by workers_mutex_
 };
 
 }  // namespace slr

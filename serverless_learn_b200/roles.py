@@ -41,6 +41,11 @@ _SIGS = {
     "slr_master_exchange_updates_wire": (C.c_int, [_p, _p, C.c_long, _p, C.c_long, C.POINTER(C.c_long)]),
     "slr_master_request_pushes": (C.c_int, [_p, _p, _p]),
     "slr_master_do_checkups": (C.c_int, [_p, _p, _p]),
+    "slr_master_enable_elastic": (C.c_int, [_p, C.c_int]),
+    "slr_master_admit_pending": (C.c_int, [_p, _p, _p]),
+    "slr_master_gossip_once": (C.c_int, [_p, _p]),
+    "slr_master_shard_of": (C.c_int, [_p, C.c_char_p]),
+    "slr_directory_remove": (C.c_int, [_p, C.c_char_p]),
     "slr_worker_create": (C.c_int, [C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_double,
                                     C.c_double, C.POINTER(_p)]),
     "slr_worker_destroy": (None, [_p]),
@@ -92,6 +97,10 @@ class Directory:
 
     def add(self, worker: "Worker"):
         assert self.L.slr_directory_add(self.p, worker.addr.encode(), worker.p) == 0
+
+    def remove(self, addr: str):
+        """The worker's server is gone (n4): calls to `addr` fail from now on."""
+        assert self.L.slr_directory_remove(self.p, addr.encode()) == 1
 
     def close(self):
         if self.p:
@@ -171,6 +180,19 @@ class Master:
 
     def do_checkups(self, fs: FileServer, d: Directory) -> int:
         return int(self.L.slr_master_do_checkups(self.p, fs.p, d.p))
+
+    # ---- elastic membership (beyond the reference, off unless enabled) ----
+    def enable_elastic(self, max_missed: int = 3):
+        assert self.L.slr_master_enable_elastic(self.p, max_missed) == 1
+
+    def admit_pending(self, fs: FileServer, d: Directory) -> int:
+        return int(self.L.slr_master_admit_pending(self.p, fs.p, d.p))
+
+    def gossip_once(self, d: Directory) -> int:
+        return int(self.L.slr_master_gossip_once(self.p, d.p))
+
+    def shard_of(self, addr: str) -> int:
+        return int(self.L.slr_master_shard_of(self.p, addr.encode()))
 
     def model(self):
         return _model_of(self.L.slr_master_handle(self.p), self.D)

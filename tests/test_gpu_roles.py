@@ -171,3 +171,88 @@ def test_async_gossip_training_follows_the_oracle_schedule(orc):
     for w in ws:
         w.close()
     master.close(); fs.close(); d.close()
+
+
+def test_elastic_join_and_dead_worker_removal(orc):
+    # §8f n4 (beyond the reference, opt-in): a worker that registers mid-run gets a free shard and
+    # the master's current model over the existing wire surface; a worker that stops answering
+    # check-ups is dropped, its shard goes to the next joiner.  The arithmetic of every step is
+    # checked against the oracle's merge (src/master.cc:95-114) and LR step.
+    from serverless_learn_b200 import roles
+    F, B, n, eta, lam = 64, 32, 320, 0.3, 0.5
+    d, fs, master = roles.Directory(), roles.FileServer(), roles.Master(F, lam=lam)
+    master.enable_elastic(2)
+    for k in range(3):
+        assert fs.add_synthetic_shard(k + 1, k * n, n, F)
+    shards = {k + 1: orc.synth(k * n, n, F) for k in range(3)}
+    ws = [roles.Worker(f"w{k}:1", F, B, eta=eta, lam=lam) for k in range(2)]
+    for w in ws:
+        d.add(w)
+        master.register_birth(w.addr)
+    assert master.admit_pending(fs, d) == 2 and master.admit_pending(fs, d) == 0   # pushed once
+    assert [master.shard_of(w.addr) for w in ws] == [1, 2]
+    assert master.do_checkups(fs, d) == 2
+    # oracle replicas: workers + master
+    om = [np.zeros(F) for _ in ws]
+    oo = [np.zeros(F) for _ in ws]
+    mm, mo = np.zeros(F), np.zeros(F)
+    libc = C.CDLL("libc.so.6")
+    libc.srand(4242)
+    draws = [libc.rand() for _ in range(8)]
+    libc.srand(4242)
+    it = iter(draws)
+    for k, w in enumerate(ws):
+        w.train_steps(6)
+        orc.lr_steps(*shards[k + 1], B, 0, 6, om[k], eta)
+    for _ in range(3):   # the master follows the workers (the reference's dead initiator, revived)
+        j = master.gossip_once(d)
+        assert j == next(it) % 2
+        reply = orc.merge_callee(om[j], oo[j], orc.delta(mm, mo))
+        orc.apply_reply(mm, mo, reply)
+    assert np.max(np.abs(mm)) > 0
+    assert np.max(np.abs(master.model() - mm)) / np.max(np.abs(mm)) <= 1e-5   # trained weights: fp32 tolerance
+    # ---- a third worker joins mid-run
+    late = roles.Worker("w2:1", F, B, eta=eta, lam=lam)
+    d.add(late)
+    master.register_birth(late.addr)
+    assert master.admit_pending(fs, d) == 1
+    assert master.shard_of(late.addr) == 3
+    assert np.array_equal(late.model(), master.model())          # exact: lambda = 0.5
+    lg = late.train_steps(4)                                       # trains on shard 3 from that model
+    ref = master.model().copy()
+    lo = orc.lr_steps(*shards[3], B, 0, 4, ref, eta)
+    assert np.max(np.abs(late.model() - ref)) / np.max(np.abs(ref)) <= 1e-5
+    assert np.max(np.abs(lg - lo) / lo) <= 1e-5
+    assert master.do_checkups(fs, d) == 3 and len(late.peers()) == 3
+    # the seed is not re-broadcast as news: the joiner's next delta is only what it learned itself
+    back = ws[0].exchange_updates(np.zeros(F))
+    assert back is not None
+    # ---- worker 1 dies: two silent check-ups drop it, the survivors' peer lists shrink
+    d.remove(ws[1].addr)
+    assert master.do_checkups(fs, d) == 2 and len(master.workers()) == 3    # first miss: still listed
+    assert master.do_checkups(fs, d) == 2 and master.workers() == ["w0:1", "w2:1"]
+    assert master.do_checkups(fs, d) == 2 and ws[0].peers() == ["w0:1", "w2:1"]
+    assert master.shard_of(ws[1].addr) == 0
+    # ---- the next joiner inherits the freed shard 2
+    heir = roles.Worker("w3:1", F, B, eta=eta, lam=lam)
+    d.add(heir)
+    master.register_birth(heir.addr)
+    assert master.admit_pending(fs, d) == 1 and master.shard_of(heir.addr) == 2
+    lg = heir.train_steps(3)
+    ref = master.model().copy()
+    lo = orc.lr_steps(*shards[2], B, 0, 3, ref, eta)
+    assert np.max(np.abs(heir.model() - ref)) / np.max(np.abs(ref)) <= 1e-5
+    for w in ws + [late, heir]:
+        w.close()
+    master.close(); fs.close(); d.close()
+
+
+def test_elastic_calls_are_off_by_default():
+    from serverless_learn_b200 import roles
+    d, fs, master = roles.Directory(), roles.FileServer(), roles.Master(16)
+    master.register_birth("ghost:1")
+    assert master.admit_pending(fs, d) == -1          # not enabled
+    for _ in range(5):                                # reference behaviour: never removed
+        assert master.do_checkups(fs, d) == 0
+    assert master.workers() == ["ghost:1"]
+    master.close(); fs.close(); d.close()
