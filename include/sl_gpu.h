@@ -79,7 +79,29 @@ int sl_debug_read(sl_handle* h, unsigned long long* out, size_t n_words);
  * swaps the new one in, so ingest overlaps training.  The byte stream is
  * kept verbatim: n_rows = floor(len / (4*(F+1))); the first n_rows*F fp32 are X
  * (row-major), the next n_rows fp32 are the labels.  size_hint = expected length
- * in bytes (0 = unknown, the buffer then grows by doubling). */
+ * in bytes (0 = unknown, the buffer then grows by doubling).
+ *
+ * Self-describing streams (the reference's files carry no format at all,
+ * src/file_server.cc:152-156): a stream that starts with the 64-byte sl_shard_header below is
+ * checked at sl_shard_end — F must match the handle, 64 + n_rows*4*(F+1) must be the stream
+ * length, and with SL_SHARD_HAS_SUMS the payload's byte sum and weighted sum (the
+ * sl_shard_checksum quantities, over the bytes after the header) must match — and the payload
+ * after the header is what gets trained on.  A mismatch fails sl_shard_end (SL_EINVAL) and keeps
+ * the previously sealed shard.  Streams without the magic are taken verbatim as before. */
+#define SL_SHARD_MAGIC "SLSHARD\1"
+#define SL_SHARD_HAS_SUMS 1u
+typedef struct sl_shard_header {   /* little-endian, 64 bytes */
+    char magic[8];                 /* SL_SHARD_MAGIC */
+    unsigned int version;          /* 1 */
+    unsigned int F;                /* features per row */
+    unsigned long long n_rows;
+    unsigned long long row0;       /* first row of the global data set held by this shard */
+    unsigned int flags;            /* SL_SHARD_HAS_SUMS */
+    unsigned int reserved0;
+    unsigned long long byte_sum;   /* sum of payload bytes mod 2^64 */
+    unsigned long long weighted;   /* sum of (i+1)*byte[i] mod 2^64, i from 0 at the payload start */
+    unsigned long long reserved1;
+} sl_shard_header;
 int sl_shard_begin(sl_handle* h, size_t size_hint);
 int sl_shard_append(sl_handle* h, const void* bytes, size_t n);
 int sl_shard_end(sl_handle* h, long long* n_rows /* nullable */);

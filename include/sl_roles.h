@@ -50,6 +50,10 @@ int slr_file_server_check_up(slr_file_server* fs); /* :122-130, no-op, returns 1
  * [row0, row0+n_rows) of the synthetic matrix; unknown numbers keep the reference's error. */
 int slr_file_server_add_synthetic_shard(slr_file_server* fs, unsigned file_num, unsigned long long row0,
                                         unsigned long long n_rows, unsigned F, unsigned long long seed);
+/* Same file, preceded by the 64-byte sl_shard_header of sl_gpu.h (F, n_rows, row0, payload sums):
+ * the receiving worker's sl_shard_end then checks what it got. */
+int slr_file_server_add_described_shard(slr_file_server* fs, unsigned file_num, unsigned long long row0,
+                                        unsigned long long n_rows, unsigned F, unsigned long long seed);
 long long slr_file_server_file_length_of(slr_file_server* fs, unsigned file_num); /* -1 unknown */
 long long slr_file_server_chunk_of(slr_file_server* fs, unsigned file_num, long long k,
                                    const void** data);

@@ -102,11 +102,13 @@ inline uint64_t splitmix64(uint64_t x) {
 }  // namespace
 
 bool FileServerCore::AddSyntheticShard(uint32_t file_num, uint64_t row0, uint64_t n_rows, uint32_t F,
-                                       uint64_t seed) {
+                                       uint64_t seed, bool with_header) {
     if (file_num == 0 || n_rows == 0 || F == 0) return false;  // file 0 stays the reference's dummy
+    const size_t hb = with_header ? sizeof(sl_shard_header) : 0;
+    const size_t payload = (size_t)n_rows * ((size_t)F + 1) * sizeof(float);
     std::string bytes;
-    bytes.resize((size_t)n_rows * ((size_t)F + 1) * sizeof(float));
-    float* X = reinterpret_cast<float*>(&bytes[0]);
+    bytes.resize(hb + payload);
+    float* X = reinterpret_cast<float*>(&bytes[hb]);
     float* y = X + (size_t)n_rows * F;
     for (uint64_t r = 0; r < n_rows; ++r) {
         float* xr = X + (size_t)r * F;
@@ -115,6 +117,25 @@ bool FileServerCore::AddSyntheticShard(uint32_t file_num, uint64_t row0, uint64_
             xr[c] = (float)(u >> 40) * (1.0f / 16777216.0f) * 2.0f - 1.0f;
         }
         y[r] = xr[0] > 0.0f ? 1.0f : 0.0f;
+    }
+    if (with_header) {
+        sl_shard_header hd;
+        memset(&hd, 0, sizeof(hd));
+        memcpy(hd.magic, SL_SHARD_MAGIC, 8);
+        hd.version = 1;
+        hd.F = F;
+        hd.n_rows = n_rows;
+        hd.row0 = row0;
+        hd.flags = SL_SHARD_HAS_SUMS;
+        const unsigned char* p = reinterpret_cast<const unsigned char*>(&bytes[hb]);
+        unsigned long long bs = 0, ws = 0;
+        for (size_t i = 0; i < payload; ++i) {
+            bs += p[i];
+            ws += (unsigned long long)(i + 1) * p[i];
+        }
+        hd.byte_sum = bs;
+        hd.weighted = ws;
+        memcpy(&bytes[0], &hd, sizeof(hd));
     }
     more_files_[file_num] = std::move(bytes);
     return true;
@@ -322,6 +343,10 @@ int slr_file_server_do_push(slr_file_server* fs, slr_directory* d, const char* r
 int slr_file_server_add_synthetic_shard(slr_file_server* fs, unsigned file_num, unsigned long long row0,
                                         unsigned long long n_rows, unsigned F, unsigned long long seed) {
     return fs->core.AddSyntheticShard(file_num, row0, n_rows, F, seed) ? 1 : 0;
+}
+int slr_file_server_add_described_shard(slr_file_server* fs, unsigned file_num, unsigned long long row0,
+                                        unsigned long long n_rows, unsigned F, unsigned long long seed) {
+    return fs && fs->core.AddSyntheticShard(file_num, row0, n_rows, F, seed, true) ? 1 : 0;
 }
 long long slr_file_server_file_length_of(slr_file_server* fs, unsigned file_num) {
     const std::string* f = fs->core.find_file(file_num);

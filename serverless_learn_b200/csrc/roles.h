@@ -83,7 +83,9 @@ class FileServerCore {
     // (proto:36-39).  File k > 0 is a training shard in the stream layout sl_shard_* expects
     // (all of X row-major fp32, then the labels): rows [row0, row0+n_rows) of the synthetic
     // matrix of SURVEY.md §8(d).  Unknown file numbers keep the reference's behaviour.
-    bool AddSyntheticShard(uint32_t file_num, uint64_t row0, uint64_t n_rows, uint32_t F, uint64_t seed);
+    // with_header: the file starts with the 64-byte sl_shard_header (sl_gpu.h) describing it
+    bool AddSyntheticShard(uint32_t file_num, uint64_t row0, uint64_t n_rows, uint32_t F, uint64_t seed,
+                           bool with_header = false);
     const std::string* find_file(uint32_t file_num) const;
     long long chunk_of(uint32_t file_num, long long k, const void** data) const;
     // FileServerImpl::DoPush :103-119 -> WorkerStub::ReceiveFile :60-87.  -1: file_num != 0

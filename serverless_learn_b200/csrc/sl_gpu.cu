@@ -130,6 +130,8 @@ struct sl_handle {
     // shard
     unsigned char* shard = nullptr;
     size_t shard_cap = 0, shard_len = 0;
+    size_t shard_off = 0;                // 64 when the sealed stream starts with an sl_shard_header
+    unsigned long long shard_row0 = 0;   // from the header (0 for raw streams)
     // incoming stream (sl_shard_begin .. sl_shard_end) lands here while `shard` stays trainable
     unsigned char* in_buf = nullptr;
     size_t in_cap = 0, in_len = 0;
@@ -436,7 +438,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
     while (done < n_steps) {
         const int n = std::min(max_per_launch, n_steps - done);
         slk::LrArgs a = plan.args;
-        a.X = reinterpret_cast<const float*>(h->shard);
+        a.X = reinterpret_cast<const float*>(h->shard + h->shard_off);
         a.y = a.X + (size_t)h->n_rows * h->F;
         a.n_rows = h->n_rows;
         a.step0 = h->step;
@@ -512,7 +514,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
 
 // one step of the simple path; sync != 0 adds the all-reduce between finish and apply
 int launch_simple_step(sl_handle* h, double* d_loss_slot, bool sync) {
-    const float* X = reinterpret_cast<const float*>(h->shard);
+    const float* X = reinterpret_cast<const float*>(h->shard + h->shard_off);
     const float* y = X + (size_t)h->n_rows * h->F;
     const long long mb = (long long)(((__int128)h->step * h->B) % h->n_rows);
     const int wpb = 8;
@@ -744,6 +746,8 @@ long long sl_get_info(sl_handle* h, const char* key) {
     if (k == "num_sms") return h->num_sms;
     if (k == "step") return h->step;
     if (k == "n_rows") return h->n_rows;
+    if (k == "shard_header") return h->shard_off ? 1 : 0;
+    if (k == "shard_row0") return (long long)h->shard_row0;
     if (k == "nranks") return h->nranks;
     if (k == "peers") return h->peer_n;
     if (k == "num_variants") return kNumVariants;
@@ -813,13 +817,49 @@ int sl_shard_end(sl_handle* h, long long* n_rows) {
     DeviceGuard dg(h->device);
     CK(h, cudaStreamSynchronize(h->copy_stream));
     CK(h, cudaStreamSynchronize(h->stream));  // no kernel may still read the outgoing shard
+    // a self-describing stream is checked before it replaces the sealed shard
+    size_t off = 0;
+    unsigned long long row0 = 0;
+    long long rows = (long long)(h->in_len / (4 * ((size_t)h->F + 1)));
+    if (h->in_len >= sizeof(sl_shard_header)) {
+        sl_shard_header hd;
+        CK(h, cudaMemcpy(&hd, h->in_buf, sizeof(hd), cudaMemcpyDeviceToHost));
+        if (memcmp(hd.magic, SL_SHARD_MAGIC, 8) == 0) {
+            h->shard_open = false;
+            const size_t in_len = h->in_len;
+            h->in_len = 0;
+            if (hd.version != 1) return fail(h, SL_EINVAL, "shard header version %u not understood", hd.version);
+            if ((int)hd.F != h->F) return fail(h, SL_EINVAL, "shard was written for F = %u, this replica has F = %d", hd.F, h->F);
+            const unsigned long long want = sizeof(hd) + hd.n_rows * 4ull * ((unsigned long long)h->F + 1);
+            if (want != in_len)
+                return fail(h, SL_EINVAL, "shard header promises %llu bytes, the stream had %zu", want, in_len);
+            if (hd.flags & SL_SHARD_HAS_SUMS) {
+                h->h_sum[0] = 0;
+                h->h_sum[1] = 0;
+                if (in_len > sizeof(hd)) {
+                    slk::checksum_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(h->in_buf + sizeof(hd), in_len - sizeof(hd), h->d_sum);
+                    h->launches++;
+                    CK(h, cudaGetLastError());
+                }
+                CK(h, cudaStreamSynchronize(h->stream));
+                if (h->h_sum[0] != hd.byte_sum || h->h_sum[1] != hd.weighted)
+                    return fail(h, SL_EINVAL, "shard payload does not match the sums in its header");
+            }
+            off = sizeof(hd);
+            row0 = hd.row0;
+            rows = (long long)hd.n_rows;
+            h->in_len = in_len;
+        }
+    }
     std::swap(h->shard, h->in_buf);
     std::swap(h->shard_cap, h->in_cap);
     h->shard_len = h->in_len;
+    h->shard_off = off;
+    h->shard_row0 = row0;
     h->in_len = 0;
     h->shard_open = false;
     h->shard_sealed = true;
-    h->n_rows = (long long)(h->shard_len / (4 * ((size_t)h->F + 1)));
+    h->n_rows = rows;
     h->step = 0;
     if (n_rows) *n_rows = h->n_rows;
     return SL_OK;
@@ -886,6 +926,8 @@ int sl_shard_synth(sl_handle* h, long long n_rows, unsigned long long row0,
     CK(h, cudaGetLastError());
     CK(h, cudaStreamSynchronize(h->stream));
     h->shard_len = bytes;
+    h->shard_off = 0;
+    h->shard_row0 = row0;
     h->n_rows = n_rows;
     h->shard_open = false;
     h->shard_sealed = true;

@@ -28,6 +28,8 @@ _SIGS = {
     "slr_file_server_check_up": (C.c_int, [_p]),
     "slr_file_server_add_synthetic_shard": (C.c_int, [_p, C.c_uint, C.c_ulonglong, C.c_ulonglong, C.c_uint,
                                                     C.c_ulonglong]),
+    "slr_file_server_add_described_shard": (C.c_int, [_p, C.c_uint, C.c_ulonglong, C.c_ulonglong, C.c_uint,
+                                                    C.c_ulonglong]),
     "slr_file_server_file_length_of": (C.c_longlong, [_p, C.c_uint]),
     "slr_file_server_chunk_of": (C.c_longlong, [_p, C.c_uint, C.c_longlong, C.POINTER(_p)]),
     "slr_master_request_pushes_sharded": (C.c_int, [_p, _p, _p]),
@@ -122,6 +124,10 @@ class FileServer:
         if n == 0:
             return np.zeros(0, np.uint8)
         return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n,))
+
+    def add_described_shard(self, file_num: int, row0: int, n_rows: int, F: int, seed: int = 0x5EED) -> bool:
+        """Like add_synthetic_shard, with the 64-byte self-describing header in front (n2)."""
+        return bool(self.L.slr_file_server_add_described_shard(self.p, file_num, row0, n_rows, F, seed))
 
     def add_synthetic_shard(self, file_num: int, row0: int, n_rows: int, F: int, seed: int = 0x5EED) -> bool:
         return bool(self.L.slr_file_server_add_synthetic_shard(self.p, file_num, row0, n_rows, F, seed))

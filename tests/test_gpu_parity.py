@@ -363,3 +363,66 @@ def test_launch_splitting_and_step_reset(sl, orc):
         assert float(np.max(np.abs(lg3 - lo3) / lo3)) <= L_TOL
         r.shard_append(y)
         assert r.shard_end() == n and r.info("step") == 0
+
+
+# ------------------------------------------------------------------ self-describing shard stream (§8f n2)
+def _described(X, y, row0=0, flags=1, F=None, n_rows=None, corrupt=False):
+    import struct
+    payload = X.astype(np.float32).tobytes() + y.astype(np.float32).tobytes()
+    b = np.frombuffer(payload, dtype=np.uint8).astype(np.uint64)
+    bs = int(b.sum(dtype=np.uint64))
+    ws = int((b * np.arange(1, b.size + 1, dtype=np.uint64)).sum(dtype=np.uint64))
+    hd = struct.pack("<8sIIQQIIQQQ", b"SLSHARD\x01", 1, X.shape[1] if F is None else F,
+                     X.shape[0] if n_rows is None else n_rows, row0, flags, 0, bs, ws, 0)
+    assert len(hd) == 64
+    if corrupt:
+        payload = payload[:100] + bytes([payload[100] ^ 1]) + payload[101:]
+    return hd + payload
+
+
+def test_described_shard_is_checked_and_trained_on(sl, orc):
+    n, F, B = 700, 260, 100
+    X, y = orc.synth(4096, n, F)
+    raw = _described(X, y, row0=4096)
+    ref = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, 9, ref, 0.2)
+    with sl.Replica(F, B, eta=0.2) as r:
+        r.shard_begin(len(raw))
+        for o in range(0, len(raw), 99991):          # chunks straddle the header and the rows
+            r.shard_append(raw[o:o + 99991])
+        assert r.shard_end() == n
+        assert r.info("shard_header") == 1 and r.info("shard_row0") == 4096
+        lg = r.train_steps(9)
+        assert w_err(r.model(), ref) <= W_TOL and np.max(np.abs(lg - lo) / lo) <= L_TOL
+        # the stream is kept verbatim (header included) for the ingest check
+        assert r.shard_bytes() == len(raw)
+        bs, ws = r.shard_checksum()
+        rb = np.frombuffer(raw, dtype=np.uint8)
+        assert (bs, ws) == (orc.bytesum(rb), orc.weighted_sum(rb)), "stream sums"
+        # a raw stream afterwards is taken as before
+        r.load_shard(X, y)
+        assert r.info("shard_header") == 0 and r.info("n_rows") == n
+
+
+@pytest.mark.parametrize("what", ["F", "n_rows", "payload", "version"])
+def test_described_shard_mismatch_keeps_the_old_shard(sl, orc, what):
+    n, F, B = 300, 64, 48
+    X, y = orc.synth(0, n, F)
+    bad = {"F": _described(X, y, F=F * 2), "n_rows": _described(X, y, n_rows=n - 1),
+           "payload": _described(X, y, corrupt=True),
+           "version": _described(X, y)[:8] + (2).to_bytes(4, "little") + _described(X, y)[12:]}[what]
+    with sl.Replica(F, B, eta=0.2) as r:
+        r.load_shard(X[:200], y[:200])
+        r.shard_begin(len(bad))
+        r.shard_append(bad)
+        with pytest.raises(sl.SlError):
+            r.shard_end()
+        assert r.info("n_rows") == 200 and r.info("shard_header") == 0    # the old shard is still there
+        ref = np.zeros(F)
+        orc.lr_steps(X[:200], y[:200], B, 0, 5, ref, 0.2)
+        r.train_steps(5)
+        assert w_err(r.model(), ref) <= W_TOL
+        # without the sums flag a flipped payload bit is not looked for
+        ok = _described(X, y, flags=0, corrupt=True)
+        r.shard_begin(len(ok)); r.shard_append(ok)
+        assert r.shard_end() == n

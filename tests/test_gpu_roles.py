@@ -256,3 +256,25 @@ def test_elastic_calls_are_off_by_default():
         assert master.do_checkups(fs, d) == 0
     assert master.workers() == ["ghost:1"]
     master.close(); fs.close(); d.close()
+
+
+def test_described_shard_through_the_file_server(orc):
+    # §8f n2: the file server writes the 64-byte header, the worker's ingest checks it
+    from serverless_learn_b200 import roles
+    F, B, n = 260, 100, 900
+    d, fs = roles.Directory(), roles.FileServer()
+    w = roles.Worker("w0:1", F, B, eta=0.2)
+    d.add(w)
+    assert fs.add_described_shard(1, 5000, n, F)
+    assert fs.file_length_of(1) == 64 + n * (F + 1) * 4
+    assert fs.do_push(d, w.addr, 1) == 1
+    X, y = orc.synth(5000, n, F)
+    ref = np.zeros(F)
+    orc.lr_steps(X, y, B, 0, 7, ref, 0.2)
+    w.train_steps(7)
+    assert np.max(np.abs(w.model() - ref)) / np.max(np.abs(ref)) <= 1e-5
+    # a shard written for another width is refused: the push reports ok=false (ReceiveFileAck.ok)
+    assert fs.add_described_shard(2, 0, n, F // 2)
+    assert fs.do_push(d, w.addr, 2) == 0
+    w.train_steps(1)          # the previous shard is still trainable
+    w.close(); fs.close(); d.close()
