@@ -27,7 +27,7 @@ __device__ __forceinline__ longlong2 ld_vol_s64x2(const long long* p) {
     return v;
 }
 
-template <int CH, int NCW, int NG>
+template <int CH, int NCW, int NG, int R>
 __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -35,11 +35,12 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     constexpr int NCT = NCW * 32;
     constexpr int GW = NCW / NG, GT = GW * 32;  // NG row groups of GW warps: a group works on one row
     static_assert(GW * NG == NCW, "row groups must divide the compute warps");
+    static_assert(R == 1 || R == 2, "a group takes one or two rows per pass");
 
     unsigned char* ring = smem;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.off_bar);   // [ns]
     uint64_t* empty = full + a.ns;                                    // [ns]
-    float* red = reinterpret_cast<float*>(smem + a.off_red);          // [2][NCW]
+    float* red = reinterpret_cast<float*>(smem + a.off_red);          // [2][NCW][R]
     float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);          // [2][zy_rows]
     long long* gsm = reinterpret_cast<long long*>(smem + a.off_gout);  // [groups][xslice] owner partial sums
 
@@ -149,7 +150,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     int red_buf = 0;
     uint32_t slot = 0, par = 0;
     long long mb = mb0;
-    float y_next = (grp < nrows_c && lane == 0) ? __ldg(a.y + (size_t)wrap(mb + lo + grp)) : 0.f;
+    // lanes 0..R-1 of every warp hold the labels of the group's next R rows
+    float y_next = (lane < R && grp * R + lane < nrows_c) ? __ldg(a.y + (size_t)wrap(mb + lo + grp * R + lane)) : 0.f;
 
     for (int s = 0; s < a.n_steps; ++s) {
         const long long mb_next = wrap(mb + a.B);
@@ -163,68 +165,98 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
             apply_total(s - 1);
             if (tid == 0) dbg_stamp(a, s, 5);
         }
-        // ring position of my group's first row of this step (the producer fills slots in row order)
-        if constexpr (NG > 1) {
-            const uint32_t q0 = (uint32_t)s * (uint32_t)nrows_c + (uint32_t)grp;
+        // ring position of my group's first row of this step (the producer fills slots in row
+        // order; a group takes R consecutive rows per pass, the groups interleave)
+        if constexpr (NG * R > 1) {
+            const uint32_t q0 = (uint32_t)s * (uint32_t)nrows_c + (uint32_t)(grp * R);
             slot = q0 % (uint32_t)ns;
             par = (q0 / (uint32_t)ns) & 1u;
         }
-        auto next_slot = [&]() {
-            if constexpr (NG == 1) {
-                if (++slot == (uint32_t)ns) { slot = 0; par ^= 1u; }
-            } else {
-                slot += NG;
-                while (slot >= (uint32_t)ns) { slot -= (uint32_t)ns; par ^= 1u; }
+        for (int i0 = grp * R; i0 < nrows_c; i0 += NG * R) {
+            float yv[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) yv[r] = __shfl_sync(0xffffffffu, y_next, r);
+            if (lane < R) {  // labels of my group's next pass (maybe the next step's first)
+                const int in = i0 + NG * R + lane;
+                if (in < nrows_c) y_next = __ldg(a.y + (size_t)wrap(mb + lo + in));
+                else if (i0 + NG * R >= nrows_c && s + 1 < a.n_steps && grp * R + lane < nrows_c)
+                    y_next = __ldg(a.y + (size_t)wrap(mb_next + lo + grp * R + lane));
             }
-        };
-        for (int i = grp; i < nrows_c; i += NG) {
-            const float yv = __shfl_sync(0xffffffffu, y_next, 0);
-            if (lane == 0) {  // label of my group's next row (maybe the next step's first)
-                if (i + NG < nrows_c) y_next = __ldg(a.y + (size_t)wrap(mb + lo + i + NG));
-                else if (s + 1 < a.n_steps && grp < nrows_c) y_next = __ldg(a.y + (size_t)wrap(mb_next + lo + grp));
+            uint32_t rb[R], sl[R];
+            bool valid[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                valid[r] = i0 + r < nrows_c;
+                uint32_t sr = slot + (uint32_t)r, pr = par;
+                if (sr >= (uint32_t)ns) { sr -= (uint32_t)ns; pr ^= 1u; }
+                sl[r] = sr;
+                rb[r] = smem_u32(ring + (size_t)sr * row_bytes);
+                if (valid[r]) mbar_wait(smem_u32(&full[sr]), pr, a.err);
             }
-            mbar_wait(smem_u32(&full[slot]), par, a.err);
-            if (a.dbg_skip) {  // diagnostics only: consume the slot without touching it
+            if (a.dbg_skip) {  // diagnostics only: consume the slots without touching them
                 __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(&empty[slot]));
-                next_slot();
-                continue;
-            }
-            const uint32_t rb = smem_u32(ring + (size_t)slot * row_bytes);
-            float acc = 0.f;
 #pragma unroll
-            for (int ch = 0; ch < CH; ++ch) {
-                if (GV(ch)) {
-                    const float4 x = lds_v4(rb + (uint32_t)GQ(ch) * 16u);
-                    acc = fmaf(x.x, w[ch].x, acc);
-                    acc = fmaf(x.y, w[ch].y, acc);
-                    acc = fmaf(x.z, w[ch].z, acc);
-                    acc = fmaf(x.w, w[ch].w, acc);
+                for (int r = 0; r < R; ++r)
+                    if (valid[r] && lane == 0) mbar_arrive(smem_u32(&empty[sl[r]]));
+            } else {
+                float acc[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    float a0 = 0.f, a1 = 0.f;
+                    if (valid[r]) {
+#pragma unroll
+                        for (int ch = 0; ch < CH; ++ch) {
+                            if (GV(ch)) {
+                                const float4 x = lds_v4(rb[r] + (uint32_t)GQ(ch) * 16u);
+                                a0 = fmaf(x.x, w[ch].x, a0);
+                                a1 = fmaf(x.y, w[ch].y, a1);
+                                a0 = fmaf(x.z, w[ch].z, a0);
+                                a1 = fmaf(x.w, w[ch].w, a1);
+                            }
+                        }
+                    }
+                    acc[r] = a0 + a1;
                 }
-            }
-            acc = warp_sum(acc);
-            float* rbuf = red + red_buf * NCW + grp * GW;
-            if (lane == 0) rbuf[warp % GW] = acc;
-            named_bar_sync(2 + grp, GT);
-            float z = 0.f;
 #pragma unroll
-            for (int k = 0; k < GW; ++k) z += rbuf[k];
-            red_buf ^= 1;
-            const float resid = sigmoid_f(z) - yv;
-            if (ct == 0 && a.loss_fix) zyb[i] = make_float2(z, yv);
+                for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-            for (int ch = 0; ch < CH; ++ch) {
-                if (GV(ch)) {
-                    const float4 x = lds_v4(rb + (uint32_t)GQ(ch) * 16u);
-                    g[ch].x = fmaf(resid, x.x, g[ch].x);
-                    g[ch].y = fmaf(resid, x.y, g[ch].y);
-                    g[ch].z = fmaf(resid, x.z, g[ch].z);
-                    g[ch].w = fmaf(resid, x.w, g[ch].w);
+                    for (int r = 0; r < R; ++r) acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], o);
                 }
+                float* rbuf = red + (red_buf * NCW + grp * GW) * R;
+                if (lane < R) rbuf[(warp % GW) * R + lane] = lane == 0 ? acc[0] : acc[R - 1];
+                named_bar_sync(2 + grp, GT);
+                red_buf ^= 1;
+                float resid[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    float z = 0.f;
+#pragma unroll
+                    for (int k = 0; k < GW; ++k) z += rbuf[k * R + r];
+                    resid[r] = valid[r] ? sigmoid_f(z) - yv[r] : 0.f;
+                    if (ct == 0 && a.loss_fix && valid[r]) zyb[i0 + r] = make_float2(z, yv[r]);
+                }
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    if (valid[r]) {
+#pragma unroll
+                        for (int ch = 0; ch < CH; ++ch) {
+                            if (GV(ch)) {
+                                const float4 x = lds_v4(rb[r] + (uint32_t)GQ(ch) * 16u);
+                                g[ch].x = fmaf(resid[r], x.x, g[ch].x);
+                                g[ch].y = fmaf(resid[r], x.y, g[ch].y);
+                                g[ch].z = fmaf(resid[r], x.z, g[ch].z);
+                                g[ch].w = fmaf(resid[r], x.w, g[ch].w);
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (valid[r] && lane == 0) mbar_arrive(smem_u32(&empty[sl[r]]));
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&empty[slot]));
-            next_slot();
+            slot += NG * R;
+            while (slot >= (uint32_t)ns) { slot -= (uint32_t)ns; par ^= 1u; }
         }
         if (tid == 0) dbg_stamp(a, s, 1);
         // ---- phase 1: this row group's partial gradient, fixed point, straight from registers to L2 ----

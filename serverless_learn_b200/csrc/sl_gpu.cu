@@ -81,9 +81,9 @@ struct Variant {
 #define SL_VARIANT(CH, R, RS, NCW, XB, WS) \
     Variant { CH, R, RS, NCW, XB, WS, 0, \
               (const void*)slk::lr_persist_kernel<CH, R, RS, NCW, (XB) != 0, WS> }
-// wide-row kernel: `r` holds the number of row groups
-#define SL_WIDE(CH, NCW, NG) \
-    Variant { CH, NG, 1, NCW, 1, 0, 1, (const void*)slk::lr_wide_kernel<CH, NCW, NG> }
+// wide-row kernel: `r` holds the number of row groups, `rs` the rows a group takes per pass
+#define SL_WIDE(CH, NCW, NG, R) \
+    Variant { CH, NG, R, NCW, 1, 0, 1, (const void*)slk::lr_wide_kernel<CH, NCW, NG, R> }
 const Variant kVariants[] = {
     SL_VARIANT(1, 16, 4, 8, 1, 0),    // 1: F <= 1024; measured best at F=1024, B/grid = 28
     SL_VARIANT(1, 16, 4, 16, 1, 0),   // 2: F <= 2048; two row groups of 16 rows
@@ -95,18 +95,25 @@ const Variant kVariants[] = {
     SL_VARIANT(8, 1, 1, 16, 0, 1),    // 8: F <= 16384, weights in shared memory
     SL_VARIANT(8, 2, 1, 8, 0, 1),     // 9: F <= 8192,  weights in shared memory
     SL_VARIANT(4, 4, 4, 14, 1, 2),    // 10: F <= 1024 as 7 row groups of 2 warps x 4 rows: 28 rows in one pass
-    SL_WIDE(10, 14, 1),               // 11: F <= 17920, wide-row kernel, 14+1 warps = 128 registers/thread
-    SL_WIDE(5, 14, 1),                // 12: F <= 8960,  wide-row kernel
-    SL_WIDE(2, 16, 1),                // 13: F <= 4096,  wide-row kernel
-    SL_WIDE(10, 14, 2),               // 14: F <= 8960,  two row groups of 7 warps
-    SL_WIDE(5, 14, 2),                // 15: F <= 4480,  two row groups of 7 warps
-    SL_WIDE(4, 16, 2),                // 16: F <= 4096,  two row groups of 8 warps
-    SL_WIDE(4, 16, 4),                // 17: F <= 2048,  four row groups of 4 warps
-    SL_WIDE(8, 12, 4),                // 18: F <= 3072,  four row groups of 3 warps
-    SL_WIDE(2, 16, 4),                // 19: F <= 1024,  four row groups of 4 warps
+    SL_WIDE(10, 14, 1, 1),            // 11: F <= 17920, wide-row kernel, 14+1 warps = 128 registers/thread
+    SL_WIDE(5, 14, 1, 1),             // 12: F <= 8960,  wide-row kernel
+    SL_WIDE(2, 16, 1, 1),             // 13: F <= 4096,  wide-row kernel
+    SL_WIDE(10, 14, 2, 1),            // 14: F <= 8960,  two row groups of 7 warps
+    SL_WIDE(5, 14, 2, 1),             // 15: F <= 4480,  two row groups of 7 warps
+    SL_WIDE(4, 16, 2, 1),             // 16: F <= 4096,  two row groups of 8 warps
+    SL_WIDE(4, 16, 4, 1),             // 17: F <= 2048,  four row groups of 4 warps
+    SL_WIDE(8, 12, 4, 1),             // 18: F <= 3072,  four row groups of 3 warps
+    SL_WIDE(2, 16, 4, 1),             // 19: F <= 1024,  four row groups of 4 warps
+    SL_WIDE(5, 14, 1, 2),             // 20: F <= 8960,  one group, two rows per pass
+    SL_WIDE(10, 14, 2, 2),            // 21: F <= 8960,  two groups, two rows per pass
+    SL_WIDE(5, 14, 2, 2),             // 22: F <= 4480,  two groups, two rows per pass
+    SL_WIDE(3, 14, 1, 2),             // 23: F <= 5376,  one group, two rows per pass
+    SL_WIDE(4, 16, 4, 2),             // 24: F <= 2048,  four groups, two rows per pass
+    SL_WIDE(2, 16, 2, 2),             // 25: F <= 2048,  two groups, two rows per pass
+    SL_WIDE(10, 14, 1, 2),            // 26: F <= 17920, one group, two rows per pass
 };
 // auto-selection: the first of these that is wide enough for F
-const int kAutoOrder[] = {1, 5, 15, 14, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
+const int kAutoOrder[] = {1, 5, 22, 20, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 }  // namespace
@@ -319,7 +326,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
         a.row_bytes = 4 * F;
         a.zy_rows = (h->B + grid - 1) / grid;
         a.xslice = 4 * ((F + 4 * grid - 1) / (4 * grid));  // columns a slice owner sums and updates
-        const size_t red_w = sizeof(float) * 2 * v.ncw;
+        const size_t red_w = sizeof(float) * 2 * v.ncw * v.rs;
         const size_t zy_w = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
         const size_t gout_w = 8 * (size_t)v.ncw * 32 * 2 + 64;  // owner partial sums: groups x slice
         const size_t fixed_w = red_w + zy_w + gout_w + 512;
@@ -327,6 +334,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
         size_t nsw = (h->smem_optin - fixed_w) / ((size_t)a.row_bytes + 16);
         nsw = std::min<size_t>(nsw, 64);
         if (h->opt_ring > 0) nsw = std::min<size_t>(nsw, (size_t)h->opt_ring);
+        if (nsw < (size_t)v.rs) { *why = "ring too short for the rows a group takes per pass"; return false; }
         a.ns = (int)nsw;
         size_t offw = (size_t)a.ns * a.row_bytes;
         offw = align_up(offw, 16); a.off_bar = (int)offw;   offw += 8 * (2 * nsw + 3);

@@ -1,4 +1,6 @@
-"""Per-step timeline of the persistent kernel (diagnostic): python tools/timeline.py [variant]"""
+"""Per-step timeline of the persistent kernel (diagnostic): python tools/timeline.py [variant] [B] [F] [rows]
+K1:  P2 = gradient staged, P3 = counter bumped, P4 = total load issued.
+K1w: P2 = partial stored + arrival bumped, P3 = all partials seen, P4 = owner published its slice."""
 import ctypes as C
 import os
 import sys
@@ -29,6 +31,8 @@ for s in range(1, 3):
     g0 = t[s, :, 0, 1].min()
     print(f"--- step {10 + s}: globaltimer ns relative to earliest CTA step start (min / median / max over CTAs)")
     for p in order:
+        if not t[s, :, p, 1].any():
+            continue  # point not stamped by this kernel
         v = t[s, :, p, 1] - g0
         print(f"  {names[p]:24s} {v.min():7d} {int(np.median(v)):7d} {v.max():7d}")
     ck = t[s, :, :, 0]
