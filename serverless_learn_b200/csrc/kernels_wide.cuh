@@ -8,10 +8,10 @@
 //     shared memory twice (dot product, then gradient) instead of holding it in registers;
 //   * that frees the shared memory a weight copy would take: three 64 KB ring slots at F=16384;
 //   * the gradient is summed in two phases THROUGH L2 WITH PLAIN STORES AND LOADS, not atomics
-//     (148 CTAs x 128 KB of L2 reductions per step measured ~100 us at F=16384): every CTA
-//     stores its s64 partial vector to `acc[c][F]`, a counter closes the phase, then the CTA that
-//     owns a slice of the vector adds the G partials of its slice (integer adds: any order gives
-//     the same bits);
+//     (148 CTAs x 128 KB of L2 reductions per step measured ~100 us at F=16384): every row group
+//     stores its fp32 partial vector to `acc[c*NG+grp][F]`, a counter closes the phase, then the
+//     CTA that owns a slice of the vector converts the partials of its slice to fixed point and
+//     adds them (integer adds: any order gives the same bits);
 //   * ONE fp64 master (`model`) per GPU: the slice owner updates it from the total (after trading
 //     the slice with the other GPUs when peers are attached: 16-byte data+flag packets over
 //     NVLink, see lr_persist_kernel) and publishes fp32 weights; a second counter closes that
@@ -21,9 +21,10 @@
 
 namespace slk {
 
-__device__ __forceinline__ longlong2 ld_vol_s64x2(const long long* p) {
-    longlong2 v;
-    asm volatile("ld.volatile.global.v2.s64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+__device__ __forceinline__ float4 ld_vol_f32x4(const float* p) {
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
     return v;
 }
 
@@ -137,15 +138,15 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
 
     // owner stage geometry: this CTA owns columns [c*L, c*L+L); a thread adds the partials
     // p = grp, grp+ngrp, ... of one pair of columns
-    const int L = a.xslice, pairs = L >> 1;
+    const int L = a.xslice, quads = L >> 2;
     const int P = G * NG;                                // partial vectors: one per row group
-    const int ngrp = max(1, min(NCT / pairs, P));
-    const int oj = tid % pairs, ogrp = tid / pairs;
-    const int oe = c * L + 2 * oj;                       // first column of my pair
+    const int ngrp = max(1, min(NCT / quads, P));
+    const int oj = tid % quads, ogrp = tid / quads;
+    const int oe = c * L + 4 * oj;                       // first of my four columns
     const bool osum = c < a.n_own && ogrp < ngrp && oe < F;
     const int ue = c * L + tid;                          // column I update as the owner
     const bool oupd = c < a.n_own && tid < L && ue < F;
-    long long* part = reinterpret_cast<long long*>(a.acc);
+    float* part = reinterpret_cast<float*>(a.acc);  // [P][Fp] fp32 partial gradients
 
     int red_buf = 0;
     uint32_t slot = 0, par = 0;
@@ -263,15 +264,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
         // (one buffer is enough: it is rewritten only after the weights of this step arrived,
         // i.e. after every owner finished reading it)
         {
-            long long* mine = part + (size_t)(c * NG + grp) * a.Fp;
+            float* mine = part + (size_t)(c * NG + grp) * a.Fp;
 #pragma unroll
-            for (int ch = 0; ch < CH; ++ch) {
-                if (GV(ch)) {
-                    longlong2* q = reinterpret_cast<longlong2*>(mine + (size_t)GQ(ch) * 4);
-                    __stcg(q, make_longlong2(to_fix(g[ch].x), to_fix(g[ch].y)));
-                    __stcg(q + 1, make_longlong2(to_fix(g[ch].z), to_fix(g[ch].w)));
-                }
-            }
+            for (int ch = 0; ch < CH; ++ch)
+                if (GV(ch)) __stcg(reinterpret_cast<float4*>(mine + (size_t)GQ(ch) * 4), g[ch]);
         }
         named_bar_sync(1, NCT);
         if (tid == 0) {
@@ -292,22 +288,28 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
         // ---- phase 2: the owner of a slice adds the G partials of it ------------------------------
         if (c < a.n_own) {
             if (osum) {
-                long long t0 = 0, t1 = 0, u0 = 0, u1 = 0;
-                const long long* src = part + oe;
+                // each partial goes to fixed point on its own, the sum is an integer sum: the same
+                // bits in any order (and the same bits as summing s64 partials would give)
+                long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+                const float* src = part + oe;
                 int pp = ogrp;
                 for (; pp + 3 * ngrp < P; pp += 4 * ngrp) {
-                    const longlong2 v0 = ld_vol_s64x2(src + (size_t)pp * a.Fp);
-                    const longlong2 v1 = ld_vol_s64x2(src + (size_t)(pp + ngrp) * a.Fp);
-                    const longlong2 v2 = ld_vol_s64x2(src + (size_t)(pp + 2 * ngrp) * a.Fp);
-                    const longlong2 v3 = ld_vol_s64x2(src + (size_t)(pp + 3 * ngrp) * a.Fp);
-                    t0 += v0.x + v2.x; t1 += v0.y + v2.y;
-                    u0 += v1.x + v3.x; u1 += v1.y + v3.y;
+                    const float4 v0 = ld_vol_f32x4(src + (size_t)pp * a.Fp);
+                    const float4 v1 = ld_vol_f32x4(src + (size_t)(pp + ngrp) * a.Fp);
+                    const float4 v2 = ld_vol_f32x4(src + (size_t)(pp + 2 * ngrp) * a.Fp);
+                    const float4 v3 = ld_vol_f32x4(src + (size_t)(pp + 3 * ngrp) * a.Fp);
+                    t0 += (to_fix(v0.x) + to_fix(v1.x)) + (to_fix(v2.x) + to_fix(v3.x));
+                    t1 += (to_fix(v0.y) + to_fix(v1.y)) + (to_fix(v2.y) + to_fix(v3.y));
+                    t2 += (to_fix(v0.z) + to_fix(v1.z)) + (to_fix(v2.z) + to_fix(v3.z));
+                    t3 += (to_fix(v0.w) + to_fix(v1.w)) + (to_fix(v2.w) + to_fix(v3.w));
                 }
                 for (; pp < P; pp += ngrp) {
-                    const longlong2 v0 = ld_vol_s64x2(src + (size_t)pp * a.Fp);
-                    t0 += v0.x; t1 += v0.y;
+                    const float4 v0 = ld_vol_f32x4(src + (size_t)pp * a.Fp);
+                    t0 += to_fix(v0.x); t1 += to_fix(v0.y); t2 += to_fix(v0.z); t3 += to_fix(v0.w);
                 }
-                *reinterpret_cast<longlong2*>(gsm + (size_t)ogrp * L + 2 * oj) = make_longlong2(t0 + u0, t1 + u1);
+                longlong2* dst = reinterpret_cast<longlong2*>(gsm + (size_t)ogrp * L + 4 * oj);
+                dst[0] = make_longlong2(t0, t1);
+                dst[1] = make_longlong2(t2, t3);
             }
             named_bar_sync(1, NCT);
             if (oupd) {

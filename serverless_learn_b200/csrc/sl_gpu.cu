@@ -113,7 +113,7 @@ const Variant kVariants[] = {
     SL_WIDE(10, 14, 1, 2),            // 26: F <= 17920, one group, two rows per pass
 };
 // auto-selection: the first of these that is wide enough for F
-const int kAutoOrder[] = {1, 5, 22, 20, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
+const int kAutoOrder[] = {1, 5, 22, 21, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 }  // namespace
@@ -328,7 +328,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
         a.xslice = 4 * ((F + 4 * grid - 1) / (4 * grid));  // columns a slice owner sums and updates
         const size_t red_w = sizeof(float) * 2 * v.ncw * v.rs;
         const size_t zy_w = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
-        const size_t gout_w = 8 * (size_t)v.ncw * 32 * 2 + 64;  // owner partial sums: groups x slice
+        const size_t gout_w = 8 * (size_t)v.ncw * 32 * 4 + 64;  // owner partial sums: groups x slice
         const size_t fixed_w = red_w + zy_w + gout_w + 512;
         if (h->smem_optin < fixed_w + 16 + (size_t)a.row_bytes) { *why = "row does not fit in shared memory"; return false; }
         size_t nsw = (h->smem_optin - fixed_w) / ((size_t)a.row_bytes + 16);
@@ -386,7 +386,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
 
 int ensure_exchange(sl_handle* h, const PersistPlan& plan) {
     const Variant& v = kVariants[plan.variant];
-    const size_t need = v.kind == 1 ? 8 * (size_t)plan.grid * v.r * plan.args.Fp   // K1w: one partial vector per row group
+    const size_t need = v.kind == 1 ? 4 * (size_t)plan.grid * v.r * plan.args.Fp   // K1w: one fp32 partial vector per row group
                                     : 8 * (size_t)3 * plan.args.krep * plan.args.Fp;
     if (h->acc_bytes < need) {
         if (h->acc) cudaFree(h->acc);
