@@ -339,8 +339,47 @@ def run_b200(args, rank, world, local_rank):
     except Exception as ex:  # the headline line must not depend on this extra
         wide = {"error": repr(ex)}
 
+    # ---- extra: config 2 — the 4-worker, 4-shard job on ONE B200 (one kernel over the four
+    # resident shards, sl_train_steps_group) next to the same job on 4 host threads ------------
+    c2 = None
+    if not multi:
+        try:
+            W2, rows2, steps2 = 4, 1 << 18, 2048
+            reps = [Replica(F, B, eta=ETA, device=local_rank) for _ in range(W2)]
+            for k, rp in enumerate(reps):
+                rp.shard_synth(rows2, row0=k * rows2)
+            Replica.train_steps_group(reps, 64, want_loss=True)
+            torch.cuda.synchronize()
+            Replica.train_steps_group(reps, steps2, want_loss=True)
+            c2_s = reps[0].last_train_ms() * 1e-3
+            c2 = {"workload": f"config 2: {W2} workers x {rows2} rows x {F} fp32 (4 GiB) resident on one B200, "
+                              f"B={B} per worker per step, gradients summed every step",
+                  "value": W2 * B * steps2 / c2_s, "unit": UNIT, "ms_per_step": 1e3 * c2_s / steps2, "steps": steps2,
+                  "variant": reps[0].info("variant"),
+                  "hbm_gbs": (W2 * 4 * (F + 1) * B + 16 * F) * steps2 / c2_s / 1e9}
+            for rp in reps:
+                rp.close()
+            import oracle
+            orc = oracle.Oracle()
+            n2 = 1 << 14
+            sh = [orc.synth(k * n2, n2, F) for k in range(W2)]
+            wv = np.zeros(F)
+            t0 = time.perf_counter()
+            orc.lr_steps_sync([x[0] for x in sh], [x[1] for x in sh], B, 0, 4, wv, ETA, threads=W2)
+            per = (time.perf_counter() - t0) / 4
+            cs = int(max(4, min(2000, 6.0 / per)))
+            t0 = time.perf_counter()
+            orc.lr_steps_sync([x[0] for x in sh], [x[1] for x in sh], B, 0, cs, wv, ETA, threads=W2)
+            dt = time.perf_counter() - t0
+            c2["cpu_4_workers"] = {"value": W2 * B * cs / dt, "unit": UNIT, "cores": W2, "kind": "port",
+                                   "sample": f"{cs} synchronous steps, {W2} worker threads x B={B} over {n2}-row shards, {dt:.1f} s"}
+        except Exception as ex:  # the headline line must not depend on this extra
+            c2 = {"error": repr(ex)}
+
     if rank == 0:
         peak, peak_src = measured_peak()
+        if c2 and "hbm_gbs" in c2:
+            c2["roofline_frac"] = c2["hbm_gbs"] / peak
         if wide and "hbm_gbs_per_gpu" in wide:
             wide["roofline_frac"] = wide["hbm_gbs_per_gpu"] / peak
         algo = algorithmic_bytes_per_step() * args.steps / k1
@@ -378,6 +417,7 @@ def run_b200(args, rank, world, local_rank):
             "gpu_launches": int(launches),
             "clocks": sampler.result(),
             "config5_shape": wide,
+            "config2": c2,
         }
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_port()

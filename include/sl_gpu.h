@@ -175,6 +175,17 @@ int sl_comm_unique_id(void* id128);
 int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128);
 int sl_allreduce_avg(sl_handle* h);
 int sl_train_steps_sync(sl_handle* h, int n_steps, double* loss_out);
+/* The same synchronous rule for W worker replicas that SHARE one GPU (BASELINE config 2: "4 workers
+ * ... same 4-shard job on 1 B200"): every step each worker takes the gradient of its own minibatch
+ * over its own shard, the W gradients are summed and all replicas apply the mean — exactly what
+ * sl_train_steps_sync computes across W GPUs, here as ONE persistent kernel over the W resident
+ * shards (no copies: the kernel reads each handle's shard in place; the step's W*B rows are spread
+ * over all SMs).  Requirements: 1 <= W <= 8, same device, F, B and eta, sealed shards with the
+ * same number of rows, F % 4 == 0 (persistent kernel only).  The model of handles[0] is the
+ * starting point; afterwards all W handles hold the new model and their step counters advance by
+ * n_steps.  loss_out (nullable): n_steps losses, each the mean over the W minibatches.
+ * No reference counterpart (the reference's workers are separate CPU processes). */
+int sl_train_steps_group(sl_handle* const* handles, int W, int n_steps, double* loss_out);
 
 /* ---- allocation-free step ------------------------------------------------------------
  * No counterpart in the reference (which never touches a GPU): one minibatch step

@@ -140,6 +140,16 @@ class Replica:
         self._ck(self._L.sl_train_steps_sync(self._h, n_steps, _d(loss) if want_loss else None))
         return loss[:n_steps] if want_loss else None
 
+    @staticmethod
+    def train_steps_group(replicas, n_steps: int, want_loss: bool = True):
+        """W worker replicas that share one GPU, trained as one job (sl_train_steps_group): every step
+        each worker's minibatch gradient over its own shard is summed and all apply the mean."""
+        first = replicas[0]
+        arr = (type(first._h) * len(replicas))(*[r._h for r in replicas])
+        loss = np.empty(max(n_steps, 1), dtype=np.float64)
+        first._ck(first._L.sl_train_steps_group(arr, len(replicas), n_steps, _d(loss) if want_loss else None))
+        return loss[:n_steps] if want_loss else None
+
     def last_train_ms(self) -> float:
         return float(self._L.sl_last_train_ms(self._h))
 

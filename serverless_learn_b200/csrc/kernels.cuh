@@ -281,7 +281,46 @@ struct LrArgs {
     // diagnostics (sl_set_option "debug_timeline"): [4 steps][grid][16] time stamps
     unsigned long long* dbg;
     int dbg_step;
+    // several worker replicas on ONE GPU trained as one job (sl_train_steps_group): the step's
+    // B = nvw*vB positions are worker 0's minibatch, then worker 1's, ...; position p belongs
+    // to worker p / vB and is row (step*vB + p % vB) mod n_rows of that worker's shard
+    // (vX[k], vy[k]; all shards hold n_rows rows).  nvw <= 1: one shard (X, y), vB = B.
+    int nvw;
+    int vB;
+    const float* vX[8];
+    const float* vy[8];
 };
+
+// where position p of the current minibatch lives: shard row pointer and label pointer;
+// `room` = how many consecutive positions from p lie in consecutive rows of the same shard
+struct RowRef {
+    const float* x;
+    const float* y;
+    long long room;
+};
+__device__ __forceinline__ RowRef locate_row(const LrArgs& a, long long mb, long long p) {
+    const float* X = a.X;
+    const float* y = a.y;
+    long long r = p, lim = a.n_rows;
+    if (a.nvw > 1) {
+        const int k = (int)(p / a.vB);
+        r = p - (long long)k * a.vB;
+        X = a.vX[k];
+        y = a.vy[k];
+        lim = a.vB - r;  // the next worker's rows start there
+    }
+    long long row = mb + r;
+    if (row >= a.n_rows) {
+        row -= a.n_rows;
+        if (row >= a.n_rows) row %= a.n_rows;
+    }
+    RowRef ref;
+    ref.x = X + (size_t)row * a.F;
+    ref.y = y + row;
+    ref.room = a.n_rows - row;  // the shard wraps there
+    if (a.nvw > 1 && lim < ref.room) ref.room = lim;
+    return ref;
+}
 
 __device__ __forceinline__ void dbg_stamp(const LrArgs& a, int s, int point) {
     if (a.dbg != nullptr && s >= a.dbg_step && s < a.dbg_step + 4) {
@@ -362,7 +401,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     const int nsl_c = (nrows_c + RS - 1) / RS;      // ... in ring slots
     const int nst_c = (nrows_c + R - 1) / R;        // ... in sub-batch stages of R rows
     const int nsb = (nst_c + RG - 1) / RG;          // sub-batches: one stage per row group
-    const long long mb0 = (long long)(((__int128)a.step0 * a.B) % a.n_rows);
+    const long long mb0 = (long long)(((__int128)a.step0 * a.vB) % a.n_rows);
     const size_t acc_stride = (size_t)KREP * Fp;    // one step buffer
     auto wrap = [&](long long v) {  // v mod n_rows; v < 2*n_rows in the common case
         if (v >= a.n_rows) {
@@ -413,14 +452,14 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     const int rc = min(RS, nrows_c - q * RS);
                     const uint32_t fb = smem_u32(&full[slot]);
                     mbar_arrive_expect_tx(fb, (uint32_t)rc * (uint32_t)row_bytes);
-                    long long g0 = wrap(mb + lo + (long long)q * RS);
+                    long long p = lo + (long long)q * RS;  // position in the minibatch
                     uint32_t dst = smem_u32(ring + (size_t)slot * slot_bytes);
                     int left = rc;
-                    while (left > 0) {  // one copy unless the rows wrap around the shard end
-                        const long long room = a.n_rows - g0;
-                        const int n = room < (long long)left ? (int)room : left;
+                    while (left > 0) {  // one copy unless the rows wrap around the shard end (or change worker)
+                        const RowRef ref = locate_row(a, mb, p);
+                        const int n = ref.room < (long long)left ? (int)ref.room : left;
                         {   // several moderate copies keep more requests in flight than one large one
-                            const unsigned char* srcb = reinterpret_cast<const unsigned char*>(a.X + (size_t)g0 * F);
+                            const unsigned char* srcb = reinterpret_cast<const unsigned char*>(ref.x);
                             uint32_t todo = (uint32_t)n * (uint32_t)row_bytes, o = 0;
                             while (todo > 0) {
                                 const uint32_t m = todo < (uint32_t)a.tma_chunk ? todo : (uint32_t)a.tma_chunk;
@@ -431,11 +470,11 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                         }
                         dst += (uint32_t)n * (uint32_t)row_bytes;
                         left -= n;
-                        g0 = 0;
+                        p += n;
                     }
                     if (++slot == (uint32_t)ns) { slot = 0; phase ^= 1u; }
                 }
-                mb = wrap(mb + a.B);
+                mb = wrap(mb + a.vB);
             }
         }
         return;
@@ -702,12 +741,12 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     // label of the row this lane finishes, fetched one stage ahead of its use
     auto load_y = [&](long long mbs, int j) -> float {
         const int i = j * R + ridx;
-        return (active && j < nst_c && i < nrows_c) ? __ldg(a.y + (size_t)wrap(mbs + lo + i)) : 0.f;
+        return (active && j < nst_c && i < nrows_c) ? __ldg(locate_row(a, mbs, lo + i).y) : 0.f;
     };
     float y_next = load_y(mb, rg);
 
     for (int s = 0; s < a.n_steps; ++s) {
-        const long long mb_next = wrap(mb + a.B);
+        const long long mb_next = wrap(mb + a.vB);
         float4 g[CH];
 #pragma unroll
         for (int ch = 0; ch < CH; ++ch) g[ch] = make_float4(0.f, 0.f, 0.f, 0.f);

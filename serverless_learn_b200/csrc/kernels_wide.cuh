@@ -49,7 +49,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     const long long lo = ((long long)c * a.B) / G;
     const long long hi = ((long long)(c + 1) * a.B) / G;
     const int nrows_c = (int)(hi - lo);
-    const long long mb0 = (long long)(((__int128)a.step0 * a.B) % a.n_rows);
+    const long long mb0 = (long long)(((__int128)a.step0 * a.vB) % a.n_rows);
     auto wrap = [&](long long v) {
         if (v >= a.n_rows) {
             v -= a.n_rows;
@@ -74,13 +74,19 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
             uint32_t slot = 0, phase = 0;
             long long mb = mb0;
             for (int s = 0; s < a.n_steps; ++s) {
-                long long grow = wrap(mb + lo);
+                const float* src = nullptr;
+                long long room = 0;  // consecutive positions left in consecutive rows of the same shard
                 for (int i = 0; i < nrows_c; ++i) {
+                    if (room == 0) {
+                        const RowRef ref = locate_row(a, mb, lo + i);
+                        src = ref.x;
+                        room = ref.room;
+                    }
                     mbar_wait(smem_u32(&empty[slot]), phase ^ 1u, a.err);
                     const uint32_t fb = smem_u32(&full[slot]);
                     mbar_arrive_expect_tx(fb, (uint32_t)row_bytes);
                     {
-                        const unsigned char* srcb = reinterpret_cast<const unsigned char*>(a.X + (size_t)grow * F);
+                        const unsigned char* srcb = reinterpret_cast<const unsigned char*>(src);
                         const uint32_t dstb = smem_u32(ring + (size_t)slot * row_bytes);
                         for (uint32_t o = 0; o < (uint32_t)row_bytes; o += (uint32_t)a.tma_chunk) {
                             const uint32_t m = min((uint32_t)a.tma_chunk, (uint32_t)row_bytes - o);
@@ -88,9 +94,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                         }
                     }
                     if (++slot == (uint32_t)ns) { slot = 0; phase ^= 1u; }
-                    if (++grow == a.n_rows) grow = 0;
+                    src += F;
+                    --room;
                 }
-                mb = wrap(mb + a.B);
+                mb = wrap(mb + a.vB);
             }
         }
         return;
@@ -152,10 +159,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     uint32_t slot = 0, par = 0;
     long long mb = mb0;
     // lanes 0..R-1 of every warp hold the labels of the group's next R rows
-    float y_next = (lane < R && grp * R + lane < nrows_c) ? __ldg(a.y + (size_t)wrap(mb + lo + grp * R + lane)) : 0.f;
+    float y_next = (lane < R && grp * R + lane < nrows_c) ? __ldg(locate_row(a, mb, lo + grp * R + lane).y) : 0.f;
 
     for (int s = 0; s < a.n_steps; ++s) {
-        const long long mb_next = wrap(mb + a.B);
+        const long long mb_next = wrap(mb + a.vB);
         float4 g[CH];
 #pragma unroll
         for (int ch = 0; ch < CH; ++ch) g[ch] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -179,9 +186,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
             for (int r = 0; r < R; ++r) yv[r] = __shfl_sync(0xffffffffu, y_next, r);
             if (lane < R) {  // labels of my group's next pass (maybe the next step's first)
                 const int in = i0 + NG * R + lane;
-                if (in < nrows_c) y_next = __ldg(a.y + (size_t)wrap(mb + lo + in));
+                if (in < nrows_c) y_next = __ldg(locate_row(a, mb, lo + in).y);
                 else if (i0 + NG * R >= nrows_c && s + 1 < a.n_steps && grp * R + lane < nrows_c)
-                    y_next = __ldg(a.y + (size_t)wrap(mb_next + lo + grp * R + lane));
+                    y_next = __ldg(locate_row(a, mb_next, lo + grp * R + lane).y);
             }
             uint32_t rb[R], sl[R];
             bool valid[R];

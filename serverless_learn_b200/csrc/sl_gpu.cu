@@ -137,6 +137,9 @@ struct sl_handle {
     // shard
     unsigned char* shard = nullptr;
     size_t shard_cap = 0, shard_len = 0;
+    int vw = 0;                          // >1 while sl_train_steps_group runs: worker replicas trained as one job
+    const float* vX[8] = {};
+    const float* vy[8] = {};
     size_t shard_off = 0;                // 64 when the sealed stream starts with an sl_shard_header
     unsigned long long shard_row0 = 0;   // from the header (0 for raw streams)
     // incoming stream (sl_shard_begin .. sl_shard_end) lands here while `shard` stays trainable
@@ -316,15 +319,18 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     slk::LrArgs& a = p->args;
     memset(&a, 0, sizeof(a));
     a.F = F;
-    a.B = h->B;
+    const long long Beff = (long long)h->B * (h->vw > 1 ? h->vw : 1);  // positions per step
+    a.B = (int)Beff;
+    a.vB = h->B;
+    a.nvw = h->vw > 1 ? h->vw : 0;
     a.Fp = F;
-    a.zy_rows = (((h->B + grid - 1) / grid + v.r - 1) / v.r) * v.r;
+    a.zy_rows = (int)((((Beff + grid - 1) / grid + v.r - 1) / v.r) * v.r);
     a.krep = !v.xb ? 1 : (F <= 1024 ? 4 : (F <= 2048 ? 2 : 1));
     a.xslice = 32;
     if (v.kind == 1) {
         a.krep = 1;
         a.row_bytes = 4 * F;
-        a.zy_rows = (h->B + grid - 1) / grid;
+        a.zy_rows = (int)((Beff + grid - 1) / grid);
         a.xslice = 4 * ((F + 4 * grid - 1) / (4 * grid));  // columns a slice owner sums and updates
         const size_t red_w = sizeof(float) * 2 * v.ncw * v.rs;
         const size_t zy_w = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
@@ -422,7 +428,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
     int max_per_launch =
         h->opt_steps_per_launch > 0 ? (int)h->opt_steps_per_launch : kMaxStepsPerLaunch;
     {   // the kernel counts its streamed rows in 32 bits
-        const long long rows_per_cta = (h->B + plan.grid - 1) / plan.grid;  // >= stages per CTA
+        const long long rows_per_cta = (plan.args.B + plan.grid - 1) / plan.grid;  // >= stages per CTA
         const long long cap = ((1ll << 31) - 1 - plan.args.ns) / std::max(1ll, rows_per_cta);
         max_per_launch = (int)std::max(1ll, std::min<long long>(max_per_launch, cap));
     }
@@ -465,7 +471,8 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         if (kVariants[plan.variant].kind == 0)
             CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 128, h->stream));
-        a.eta_over_b = h->eta / (double)h->B;
+        a.eta_over_b = h->eta / (double)a.B;
+        for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; }
         a.hold_refills = h->opt_hold != 0 ? 1 : 0;
         a.rotate_reduce = h->opt_rotate != 0 ? 1 : 0;
         a.poll_pause = (int)h->opt_poll_pause;
@@ -508,7 +515,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
     }
     if (want_loss) {
         slk::loss_finish_kernel<<<(n_steps + 255) / 256, 256, 0, h->stream>>>(
-            h->loss_fix, h->d_loss, n_steps, 1.0 / (double)h->B);
+            h->loss_fix, h->d_loss, n_steps, 1.0 / (double)plan.args.B);
         h->launches++;
         CK(h, cudaGetLastError());
     }
@@ -965,6 +972,54 @@ int sl_train_steps_sync(sl_handle* h, int n_steps, double* loss_out) {
     if (!h) return SL_EINVAL;
     std::lock_guard<std::mutex> lk(h->mu);
     return train_impl(h, n_steps, loss_out, true);
+}
+
+int sl_train_steps_group(sl_handle* const* handles, int W, int n_steps, double* loss_out) {
+    if (!handles || W < 1 || W > 8) return fail(nullptr, SL_EINVAL, "W must be 1..8");
+    for (int k = 0; k < W; ++k) {
+        if (!handles[k]) return fail(nullptr, SL_EINVAL, "handle %d is NULL", k);
+        for (int j = 0; j < k; ++j)
+            if (handles[j] == handles[k]) return fail(handles[0], SL_EINVAL, "handle %d is listed twice", k);
+    }
+    sl_handle* h = handles[0];
+    // take every handle's lock, in address order so that two group calls cannot deadlock
+    std::vector<sl_handle*> order(handles, handles + W);
+    std::sort(order.begin(), order.end());
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (sl_handle* o : order) locks.emplace_back(o->mu);
+    for (int k = 0; k < W; ++k) {
+        sl_handle* w = handles[k];
+        if (w->device != h->device || w->F != h->F || w->B != h->B || w->eta != h->eta)
+            return fail(h, SL_EINVAL, "worker %d differs from worker 0 in device, F, B or eta", k);
+        if (!w->shard_sealed || w->n_rows <= 0) return fail(h, SL_ESTATE, "worker %d has no sealed shard", k);
+        if (w->n_rows != h->n_rows)
+            return fail(h, SL_EINVAL, "worker %d holds %lld rows, worker 0 holds %lld: shards must be equal",
+                        k, w->n_rows, h->n_rows);
+        if (w->step != h->step) return fail(h, SL_ESTATE, "worker %d is at step %lld, worker 0 at %lld", k, w->step, h->step);
+        if (((uintptr_t)(w->shard + w->shard_off) & 15) != 0) return fail(h, SL_EINVAL, "worker %d: shard not 16-byte aligned", k);
+    }
+    if (n_steps < 0) return fail(h, SL_EINVAL, "n_steps < 0");
+    if (n_steps == 0) return SL_OK;
+    DeviceGuard dg(h->device);
+    for (int k = 1; k < W; ++k) CK(h, cudaStreamSynchronize(handles[k]->stream));  // their shards are settled
+    for (int k = 0; k < W; ++k) {
+        h->vX[k] = reinterpret_cast<const float*>(handles[k]->shard + handles[k]->shard_off);
+        h->vy[k] = h->vX[k] + (size_t)handles[k]->n_rows * h->F;
+    }
+    h->vw = W;
+    const long long saved_path = h->opt_path;
+    if (h->opt_path == 0) h->opt_path = 1;  // the simple path has no multi-shard mode: fail instead of falling back
+    int rc = h->opt_path == 1 ? train_impl(h, n_steps, loss_out, false)
+                              : fail(h, SL_EINVAL, "sl_train_steps_group runs on the persistent kernel only");
+    h->opt_path = saved_path;
+    h->vw = 0;
+    if (rc) return rc;
+    for (int k = 1; k < W; ++k) {  // every replica leaves with the new model (old is untouched, as in sl_train_steps)
+        CK(h, cudaMemcpyAsync(handles[k]->model, h->model, sizeof(double) * (size_t)h->D, cudaMemcpyDeviceToDevice, h->stream));
+        handles[k]->step = h->step;
+    }
+    CK(h, cudaStreamSynchronize(h->stream));
+    return SL_OK;
 }
 
 float sl_last_train_ms(sl_handle* h) { return h ? h->last_ms : -1.f; }

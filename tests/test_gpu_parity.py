@@ -427,3 +427,52 @@ def test_described_shard_mismatch_keeps_the_old_shard(sl, orc, what):
         ok = _described(X, y, flags=0, corrupt=True)
         r.shard_begin(len(ok)); r.shard_append(ok)
         assert r.shard_end() == n
+
+
+# ------------------------------------------------------------------ W workers sharing one GPU (config 2)
+@pytest.mark.parametrize("W,n,F,B,variant", [
+    (4, 640, 64, 48, 0),        # B not a multiple of the ring slot: slots straddle two workers
+    (4, 1000, 1024, 256, 1),    # config-2 shape in small, headline variant
+    (3, 500, 260, 100, 0),      # ragged: minibatches wrap inside every shard
+    (2, 400, 4096, 160, 0),     # wide rows: K1w row groups
+    (8, 96, 16, 7, 0),          # many workers, tiny batches
+    (4, 300, 2048, 90, 17),     # K1w, four row groups
+    (2, 200, 16384, 64, 11),    # K1w at full width
+])
+def test_group_of_workers_on_one_gpu_equals_sync_loop(sl, orc, W, n, F, B, variant):
+    steps, eta = 9, 0.2
+    shards = [orc.synth(k * n, n, F) for k in range(W)]
+    w = np.zeros(F)
+    lo = orc.lr_steps_sync([s[0] for s in shards], [s[1] for s in shards], B, 0, steps, w, eta)
+    reps = [sl.Replica(F, B, eta=eta) for _ in range(W)]
+    try:
+        for r, (X, y) in zip(reps, shards):
+            r.load_shard(X, y)
+        reps[0].set_option("variant", variant)
+        lg = np.concatenate([sl.Replica.train_steps_group(reps, 4), sl.Replica.train_steps_group(reps, steps - 4)])
+        assert reps[0].info("path") == 1
+        for r in reps:
+            assert np.array_equal(r.model(), reps[0].model())        # every replica leaves with the new model
+            assert r.info("step") == steps
+        assert w_err(reps[0].model(), w) <= W_TOL and np.max(np.abs(lg - lo) / lo) <= L_TOL
+    finally:
+        for r in reps:
+            r.close()
+
+
+def test_group_equals_one_worker_when_W_is_1_and_rejects_mismatches(sl, orc):
+    n, F, B = 300, 64, 48
+    X, y = orc.synth(0, n, F)
+    with sl.Replica(F, B, eta=0.2) as a, sl.Replica(F, B, eta=0.2) as b, sl.Replica(F, B, eta=0.2) as c:
+        a.load_shard(X, y); b.load_shard(X, y)
+        la = sl.Replica.train_steps_group([a], 7)
+        lb = b.train_steps(7)
+        assert np.array_equal(la, lb) and np.array_equal(a.model(), b.model())
+        c.load_shard(X[:200], y[:200])
+        with pytest.raises(sl.SlError):
+            sl.Replica.train_steps_group([a, c], 1)          # unequal shards
+        with pytest.raises(sl.SlError):
+            sl.Replica.train_steps_group([a, a], 1)          # the same handle twice
+        c.load_shard(X, y)
+        with pytest.raises(sl.SlError):
+            sl.Replica.train_steps_group([a, c], 1)          # a is at step 7, c at step 0
