@@ -114,6 +114,9 @@ int slr_worker_exchange_updates(slr_worker* w, const double* delta, int n, doubl
 /* one iteration of periodically_gossip (:194-219) without the sleep: partner = rand() % N over
  * the peer list; returns the partner index, -1 when there is no peer or the partner cannot be
  * reached (repair R7: the round is skipped), -2 on a GPU error */
+/* W workers of this process that share one GPU take n_steps synchronous steps as one job
+ * (sl_train_steps_group: BASELINE config 2, "4 workers ... same 4-shard job on 1 B200").  1 = ok. */
+int slr_workers_train_steps_group(slr_worker* const* ws, int W, int n_steps, double* loss_out);
 int slr_worker_gossip_once(slr_worker* w, slr_directory* d);
 /* one iteration of simulate_training (:221-231) without the sleep: the reference's +1 ... */
 int slr_worker_train_tick(slr_worker* w);

@@ -43,6 +43,7 @@ _SIGS = {
     "slr_master_exchange_updates_wire": (C.c_int, [_p, _p, C.c_long, _p, C.c_long, C.POINTER(C.c_long)]),
     "slr_master_request_pushes": (C.c_int, [_p, _p, _p]),
     "slr_master_do_checkups": (C.c_int, [_p, _p, _p]),
+    "slr_workers_train_steps_group": (C.c_int, [C.POINTER(_p), C.c_int, C.c_int, _dp]),
     "slr_master_enable_elastic": (C.c_int, [_p, C.c_int]),
     "slr_master_admit_pending": (C.c_int, [_p, _p, _p]),
     "slr_master_gossip_once": (C.c_int, [_p, _p]),
@@ -207,6 +208,15 @@ class Master:
         if self.p:
             self.L.slr_master_destroy(self.p)
             self.p = _p()
+
+
+def train_steps_group(workers, n: int):
+    """W workers sharing one GPU take n synchronous steps as one kernel (config 2); returns the losses."""
+    L = load()
+    arr = (_p * len(workers))(*[w.p for w in workers])
+    loss = np.empty(max(n, 1))
+    assert L.slr_workers_train_steps_group(arr, len(workers), n, _d(loss)) == 1
+    return loss[:n]
 
 
 class Worker:

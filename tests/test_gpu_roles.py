@@ -278,3 +278,27 @@ def test_described_shard_through_the_file_server(orc):
     assert fs.do_push(d, w.addr, 2) == 0
     w.train_steps(1)          # the previous shard is still trainable
     w.close(); fs.close(); d.close()
+
+
+def test_config2_four_workers_on_one_gpu(orc):
+    # BASELINE config 2 in small: master + 4 workers + file server in one process, every worker gets
+    # its own shard through DoPush/ReceiveFile, then the four train synchronously as ONE kernel
+    from serverless_learn_b200 import roles
+    F, B, n, W, steps = 128, 64, 512, 4, 10
+    d, fs, master = roles.Directory(), roles.FileServer(), roles.Master(F)
+    ws = [roles.Worker(f"w{k}:1", F, B, eta=0.2) for k in range(W)]
+    for k, w in enumerate(ws):
+        d.add(w)
+        master.register_birth(w.addr)
+        assert fs.add_described_shard(k + 1, k * n, n, F)
+    assert master.request_pushes_sharded(fs, d) == W
+    lg = roles.train_steps_group(ws, steps)
+    shards = [orc.synth(k * n, n, F) for k in range(W)]
+    ref = np.zeros(F)
+    lo = orc.lr_steps_sync([s[0] for s in shards], [s[1] for s in shards], B, 0, steps, ref, 0.2)
+    for w in ws:
+        assert np.max(np.abs(w.model() - ref)) / np.max(np.abs(ref)) <= 1e-5
+    assert np.max(np.abs(lg - lo) / lo) <= 1e-5
+    for w in ws:
+        w.close()
+    master.close(); fs.close(); d.close()
