@@ -144,15 +144,11 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     };
 
     // owner stage geometry: this CTA owns columns [c*L, c*L+L); a thread adds the partials
-    // p = grp, grp+ngrp, ... of one pair of columns
+    // p = grp, grp+ngrp, ... of four columns
     const int L = a.xslice, quads = L >> 2;
     const int P = G * NG;                                // partial vectors: one per row group
     const int ngrp = max(1, min(NCT / quads, P));
-    const int oj = tid % quads, ogrp = tid / quads;
-    const int oe = c * L + 4 * oj;                       // first of my four columns
-    const bool osum = c < a.n_own && ogrp < ngrp && oe < F;
-    const int ue = c * L + tid;                          // column I update as the owner
-    const bool oupd = c < a.n_own && tid < L && ue < F;
+    // (a slice wider than the CTA — small grids — is walked in several rounds)
     float* part = reinterpret_cast<float*>(a.acc);  // [P][Fp] fp32 partial gradients
 
     int red_buf = 0;
@@ -294,7 +290,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
         if (tid == 0) dbg_stamp(a, s, 3);
         // ---- phase 2: the owner of a slice adds the G partials of it ------------------------------
         if (c < a.n_own) {
-            if (osum) {
+            for (int u = tid; u < quads * ngrp; u += NCT) {
+                const int oj = u % quads, ogrp = u / quads;
+                const int oe = c * L + 4 * oj;  // first of my four columns
+                if (oe >= F) continue;
                 // each partial goes to fixed point on its own, the sum is an integer sum: the same
                 // bits in any order (and the same bits as summing s64 partials would give)
                 long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
@@ -319,9 +318,11 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                 dst[1] = make_longlong2(t2, t3);
             }
             named_bar_sync(1, NCT);
-            if (oupd) {
+            for (int t = tid; t < L; t += NCT) {
+                const int ue = c * L + t;  // column I update as the owner
+                if (ue >= F) break;
                 long long tot = 0;
-                for (int k = 0; k < ngrp; ++k) tot += gsm[(size_t)k * L + tid];
+                for (int k = 0; k < ngrp; ++k) tot += gsm[(size_t)k * L + t];
                 if (a.nranks > 1) {  // trade the slice total with the other GPUs
                     const unsigned xflag = a.xflag0 + (unsigned)s + 1u;
                     const size_t half = (size_t)(xflag & 1u) * (size_t)a.nranks * (size_t)F;

@@ -334,7 +334,8 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
         a.xslice = 4 * ((F + 4 * grid - 1) / (4 * grid));  // columns a slice owner sums and updates
         const size_t red_w = sizeof(float) * 2 * v.ncw * v.rs;
         const size_t zy_w = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
-        const size_t gout_w = 8 * (size_t)v.ncw * 32 * 4 + 64;  // owner partial sums: groups x slice
+        // owner partial sums: groups x slice (a slice wider than the CTA's threads: one group)
+        const size_t gout_w = std::max<size_t>(8 * (size_t)v.ncw * 32 * 4, 8 * (size_t)a.xslice) + 64;
         const size_t fixed_w = red_w + zy_w + gout_w + 512;
         if (h->smem_optin < fixed_w + 16 + (size_t)a.row_bytes) { *why = "row does not fit in shared memory"; return false; }
         size_t nsw = (h->smem_optin - fixed_w) / ((size_t)a.row_bytes + 16);

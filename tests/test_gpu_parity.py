@@ -204,6 +204,14 @@ def test_lr_grid_sizes(sl, orc, grid):
     assert ew <= W_TOL and el <= L_TOL, (ew, el, info)
 
 
+@pytest.mark.parametrize("variant,F,grid", [(22, 4096, 3), (11, 16384, 1), (21, 8192, 5), (20, 2048, 2), (11, 16384, 19)])
+def test_lr_wide_rows_on_small_grids(sl, orc, variant, F, grid):
+    # the slice a CTA owns is wider than its thread count: the owner stage walks it in rounds
+    ew, el, info, _, _ = _run_case(sl, orc, 300, F, 90, 6, 0.2, 1, variant=variant, grid=grid)
+    assert info == (1, variant, grid)
+    assert ew <= W_TOL and el <= L_TOL, (ew, el, info)
+
+
 def test_lr_unaligned_F_uses_simple_path(sl, orc):
     ew, el, info, _, _ = _run_case(sl, orc, 333, 77, 50, 9, 0.2, 0)
     assert info[0] == 2
