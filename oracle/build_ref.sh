@@ -9,8 +9,9 @@
 # where they lie under /root/reference, applies only the listed repairs with sed,
 # and compiles them inside the thin wrappers of ref_shim.cc against a 20-line
 # stand-in for the generated `Update` message (delta_size / delta / add_delta).
-# Nothing from the reference is committed: the extracted fragments and the built
-# library go to oracle/_ref/, which is git-ignored (but travels to the GPU box).
+# Nothing from the reference is kept: the extracted fragments live in a temporary
+# directory for the duration of the compile only; the built library alone goes to
+# oracle/_ref/, which is git-ignored (but travels to the GPU box).
 #
 #   fragment            reference lines                     repair
 #   file0_consts.inc    src/file_server.cc:40,43,46         none
@@ -31,15 +32,18 @@ if [ ! -f "$REF/master.cc" ]; then
   exit 0
 fi
 mkdir -p "$OUT"
-sed -n '40p;43p;46p' "$REF/file_server.cc" > "$OUT/file0_consts.inc"
-sed -n '152,156p' "$REF/file_server.cc" > "$OUT/file0_body.inc"
-sed -n '58,60p' "$REF/master.cc" > "$OUT/state.inc"
-sed -n '99,110p' "$REF/master.cc" | sed 's/updates->/update->/' > "$OUT/merge_body.inc"
-sed -n '155,162p;164p' "$REF/worker.cc" | sed 's/update_back->/update_back./g' > "$OUT/apply_body.inc"
-sed -n '205,208p' "$REF/worker.cc" | sed 's/update->/update./' > "$OUT/delta_body.inc"
-sed -n '215p' "$REF/worker.cc" > "$OUT/oldcopy_body.inc"
-sed -n '225,227p' "$REF/worker.cc" > "$OUT/tick_body.inc"
+rm -f "$OUT"/*.inc
+FRAG="$(mktemp -d)"
+trap 'rm -rf "$FRAG"' EXIT
+sed -n '40p;43p;46p' "$REF/file_server.cc" > "$FRAG/file0_consts.inc"
+sed -n '152,156p' "$REF/file_server.cc" > "$FRAG/file0_body.inc"
+sed -n '58,60p' "$REF/master.cc" > "$FRAG/state.inc"
+sed -n '99,110p' "$REF/master.cc" | sed 's/updates->/update->/' > "$FRAG/merge_body.inc"
+sed -n '155,162p;164p' "$REF/worker.cc" | sed 's/update_back->/update_back./g' > "$FRAG/apply_body.inc"
+sed -n '205,208p' "$REF/worker.cc" | sed 's/update->/update./' > "$FRAG/delta_body.inc"
+sed -n '215p' "$REF/worker.cc" > "$FRAG/oldcopy_body.inc"
+sed -n '225,227p' "$REF/worker.cc" > "$FRAG/tick_body.inc"
 # -O0, no -march: the reference's own flags are `-std=c++11` and nothing else
 # (src/Makefile:8); file 0 is built with -O2 only to keep the 1e8-iteration loop short.
-g++ -std=c++11 -O2 -fPIC -shared -ffp-contract=off -w -I"$OUT" "$HERE/ref_shim.cc" -o "$OUT/libsl_ref.so"
+g++ -std=c++11 -O2 -fPIC -shared -ffp-contract=off -w -I"$FRAG" "$HERE/ref_shim.cc" -o "$OUT/libsl_ref.so"
 echo "built $OUT/libsl_ref.so"
