@@ -1,5 +1,5 @@
 // ref_shim.cc — thin wrappers around fragments of the reference lifted at build
-// time by oracle/build_ref.sh into oracle/_ref/*.inc.  TEST INFRASTRUCTURE ONLY.
+// time by oracle/build_ref.sh into a temporary directory (removed after the compile).  TEST INFRASTRUCTURE ONLY.
 // This file holds no reference code: each `#include "x.inc"` below is replaced by
 // the reference's own statements (with the repairs build_ref.sh lists) when the
 // library is built in a container that has /root/reference.
