@@ -264,6 +264,7 @@ struct LrArgs {
     int tma_chunk;         // bytes per bulk copy (a row block is fetched as several copies on one mbarrier)
     int dbg_skip;          // diagnostics: K1w skips the per-row maths (measures the bare TMA ring rate)
     int poll_pause;        // SM cycles the exchange thread waits after its bump before it starts polling
+    int relaxed_signal;    // experiment: bump the arrival counter with a relaxed red after the bulk reduction completed
     int rotate_reduce;     // 1: CTA-dependent start line of the bulk reduction
     int hold_refills;      // 1: the producer re-arms slots only after the step's reduction is released
     int direct_total;      // 1: threads read the gradient total straight from L2 instead of a TMA load into smem
@@ -511,7 +512,10 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     dbg_stamp(a, s, 7);
                     asm volatile("fence.proxy.async;" ::: "memory");
                 }
-                red_release_add_u32(a.counter, 1u);
+                if (XB && a.relaxed_signal)
+                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(a.counter), "r"(1u) : "memory");
+                else
+                    red_release_add_u32(a.counter, 1u);
                 mbar_arrive(smem_u32(rgo));  // the producer may refill what step s freed
                 dbg_stamp(a, s, 3);
                 const unsigned want = (unsigned)G * (unsigned)(s + 1);
