@@ -275,6 +275,30 @@ def test_lr_full_size_properties(sl):
     assert float(np.max(np.abs(l1 - l2) / l2)) <= L_TOL
 
 
+def test_lr_config5_full_size_per_gpu(sl, orc):
+    # config 5's per-GPU shard at full size: 2^20 rows x 16384 fp32 = 64 GiB resident, B = 16384.
+    # Properties that need no oracle, plus oracle parity on the first minibatches (the oracle only
+    # needs the rows a step touches: rows [0, 3B) generated on the host).
+    import torch
+    if torch.cuda.mem_get_info()[1] < 100 * (1 << 30):
+        pytest.skip("needs a GPU with > 100 GiB")
+    n, F, B, steps = 1 << 20, 16384, 16384, 72     # 72 steps cross the epoch boundary at step 64
+    with sl.Replica(F, B) as r:
+        r.shard_synth(n)
+        l1 = r.train_steps(steps)
+        w1 = r.model()
+        assert np.all(np.isfinite(l1)) and abs(l1[0] - np.log(2)) < 1e-6 and l1[-1] < l1[0]
+        assert r.info("variant") == 11 and r.info("path") == 1
+        r.set_option("step", 0)
+        r.set_state(np.zeros(F), np.zeros(F))
+        l2 = r.train_steps(steps)
+        assert np.array_equal(l1, l2) and np.array_equal(w1, r.model())    # run-to-run identical
+    X, y = orc.synth(0, 3 * B, F)
+    ref = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, 3, ref, 0.1)
+    assert float(np.max(np.abs(l1[:3] - lo) / lo)) <= L_TOL
+
+
 def test_sync_mode_single_rank_equals_local_steps(sl, orc):
     # sl_train_steps_sync with a 1-rank NCCL communicator: same numbers as the oracle; exercises
     # the dlopen'd NCCL, the all-reduce of the gradient sum and the averaged update
