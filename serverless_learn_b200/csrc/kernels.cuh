@@ -264,6 +264,7 @@ struct LrArgs {
     int tma_chunk;         // bytes per bulk copy (a row block is fetched as several copies on one mbarrier)
     int dbg_skip;          // diagnostics: K1w skips the per-row maths (measures the bare TMA ring rate)
     int poll_pause;        // SM cycles the exchange thread waits after its bump before it starts polling
+    int block_rows;        // K1w: 1 = a CTA takes a contiguous block of the minibatch instead of every G-th row
     int relaxed_signal;    // experiment: bump the arrival counter with a relaxed red after the bulk reduction completed
     int rotate_reduce;     // 1: CTA-dependent start line of the bulk reduction
     int hold_refills;      // 1: the producer re-arms slots only after the step's reduction is released

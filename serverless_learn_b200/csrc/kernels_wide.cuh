@@ -46,9 +46,14 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     long long* gsm = reinterpret_cast<long long*>(smem + a.off_gout);  // [groups][xslice] owner partial sums
 
     const int F = a.F, ns = a.ns, row_bytes = a.row_bytes;
-    const long long lo = ((long long)c * a.B) / G;
+    // this CTA's positions of every minibatch: every G-th position (at any moment the grid then
+    // reads one contiguous window of the shard: measured 4-5 % faster at F >= 8192 than giving every
+    // CTA its own contiguous block, which is what `block_rows` restores)
+    const bool ilv = a.block_rows == 0;
+    const long long lo = ilv ? c : ((long long)c * a.B) / G;
     const long long hi = ((long long)(c + 1) * a.B) / G;
-    const int nrows_c = (int)(hi - lo);
+    const int nrows_c = ilv ? (int)((a.B - c + G - 1) / G) : (int)(hi - ((long long)c * a.B) / G);
+    const int pstride = ilv ? G : 1;
     const long long mb0 = (long long)(((__int128)a.step0 * a.vB) % a.n_rows);
     auto wrap = [&](long long v) {
         if (v >= a.n_rows) {
@@ -78,9 +83,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                 long long room = 0;  // consecutive positions left in consecutive rows of the same shard
                 for (int i = 0; i < nrows_c; ++i) {
                     if (room == 0) {
-                        const RowRef ref = locate_row(a, mb, lo + i);
+                        const RowRef ref = locate_row(a, mb, lo + (long long)i * pstride);
                         src = ref.x;
-                        room = ref.room;
+                        room = ilv ? 1 : ref.room;
                     }
                     mbar_wait(smem_u32(&empty[slot]), phase ^ 1u, a.err);
                     const uint32_t fb = smem_u32(&full[slot]);
@@ -155,7 +160,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     uint32_t slot = 0, par = 0;
     long long mb = mb0;
     // lanes 0..R-1 of every warp hold the labels of the group's next R rows
-    float y_next = (lane < R && grp * R + lane < nrows_c) ? __ldg(locate_row(a, mb, lo + grp * R + lane).y) : 0.f;
+    float y_next = (lane < R && grp * R + lane < nrows_c) ? __ldg(locate_row(a, mb, lo + (long long)(grp * R + lane) * pstride).y) : 0.f;
 
     for (int s = 0; s < a.n_steps; ++s) {
         const long long mb_next = wrap(mb + a.vB);
@@ -182,9 +187,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
             for (int r = 0; r < R; ++r) yv[r] = __shfl_sync(0xffffffffu, y_next, r);
             if (lane < R) {  // labels of my group's next pass (maybe the next step's first)
                 const int in = i0 + NG * R + lane;
-                if (in < nrows_c) y_next = __ldg(locate_row(a, mb, lo + in).y);
+                if (in < nrows_c) y_next = __ldg(locate_row(a, mb, lo + (long long)in * pstride).y);
                 else if (i0 + NG * R >= nrows_c && s + 1 < a.n_steps && grp * R + lane < nrows_c)
-                    y_next = __ldg(locate_row(a, mb_next, lo + grp * R + lane).y);
+                    y_next = __ldg(locate_row(a, mb_next, lo + (long long)(grp * R + lane) * pstride).y);
             }
             uint32_t rb[R], sl[R];
             bool valid[R];

@@ -168,7 +168,7 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0, opt_persist_l2 = 0, opt_poll_pause = 0, opt_dbg_skip = 0, opt_tma_chunk = 0, opt_relaxed_signal = 0;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0, opt_persist_l2 = 0, opt_poll_pause = 0, opt_dbg_skip = 0, opt_tma_chunk = 0, opt_relaxed_signal = 0, opt_block_rows = 0;
     bool l2_window_set = false;
     unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
@@ -478,6 +478,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         a.rotate_reduce = h->opt_rotate != 0 ? 1 : 0;
         a.poll_pause = (int)h->opt_poll_pause;
         a.relaxed_signal = h->opt_relaxed_signal != 0 ? 1 : 0;
+        a.block_rows = h->opt_block_rows != 0 ? 1 : 0;
         a.dbg_skip = h->opt_dbg_skip != 0 ? 1 : 0;
         a.tma_chunk = h->opt_tma_chunk > 0 ? (int)((h->opt_tma_chunk + 15) / 16 * 16) : (1 << 20);
         a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && kVariants[plan.variant].kind == 0 && plan.args.krep <= 4) ? 1 : 0;
@@ -742,6 +743,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "rotate_reduce") h->opt_rotate = value;
     else if (k == "persist_l2") h->opt_persist_l2 = value;
     else if (k == "relaxed_signal") h->opt_relaxed_signal = value;
+    else if (k == "block_rows") h->opt_block_rows = value;
     else if (k == "poll_pause") h->opt_poll_pause = value;
     else if (k == "debug_skip_compute") h->opt_dbg_skip = value;
     else if (k == "tma_chunk") h->opt_tma_chunk = value;
