@@ -3,9 +3,10 @@
 //
 // Same row ring and fixed-point arithmetic as lr_persist_kernel (kernels.cuh), with the roles laid
 // out for long steps:
-//   * every compute warp works on the SAME row (one row group); a thread keeps the fp32 weights
-//     and the gradient of its CH float4 column chunks in registers and reads the row from
-//     shared memory twice (dot product, then gradient) instead of holding it in registers;
+//   * the compute warps form NG row groups; all warps of a group work on the SAME R rows (R = 1
+//     or 2 per pass); a thread keeps the fp32 weights and the gradient of its CH float4 column
+//     chunks in registers and reads the row from shared memory twice (dot product, then
+//     gradient) instead of holding it in registers;
 //   * that frees the shared memory a weight copy would take: three 64 KB ring slots at F=16384;
 //   * the gradient is summed in two phases THROUGH L2 WITH PLAIN STORES AND LOADS, not atomics
 //     (148 CTAs x 128 KB of L2 reductions per step measured ~100 us at F=16384): every row group
