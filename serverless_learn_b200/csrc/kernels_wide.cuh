@@ -37,7 +37,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     constexpr int NCT = NCW * 32;
     constexpr int GW = NCW / NG, GT = GW * 32;  // NG row groups of GW warps: a group works on one row
     static_assert(GW * NG == NCW, "row groups must divide the compute warps");
-    static_assert(R == 1 || R == 2, "a group takes one or two rows per pass");
+    static_assert(R >= 1 && R <= 4, "a group takes one to four rows per pass");
 
     unsigned char* ring = smem;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.off_bar);   // [ns]
@@ -233,7 +233,13 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                     for (int r = 0; r < R; ++r) acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], o);
                 }
                 float* rbuf = red + (red_buf * NCW + grp * GW) * R;
-                if (lane < R) rbuf[(warp % GW) * R + lane] = lane == 0 ? acc[0] : acc[R - 1];
+                {
+                    float mine = acc[0];  // lane r publishes the group's partial dot product of row r
+#pragma unroll
+                    for (int r = 1; r < R; ++r)
+                        if (lane == r) mine = acc[r];
+                    if (lane < R) rbuf[(warp % GW) * R + lane] = mine;
+                }
                 named_bar_sync(2 + grp, GT);
                 red_buf ^= 1;
                 float resid[R];
