@@ -74,36 +74,34 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
     __syncthreads();
 
     // =========================================================================== producer
+    // Lane l of the producer warp owns ring slot l (ns <= 32): it fetches rows l, l+ns, l+2ns, ...
+    // of this CTA's row sequence over the whole launch.  Issuing a row costs one thread ~600
+    // cycles (wait, address, expect_tx, copy); in parallel lanes that cost no longer bounds
+    // narrow rows.  A slot's fills are all issued by the same lane, in order, and (ns is a multiple
+    // of NG*R) consumed by the same row group, in order, so the parity waits on its barriers never
+    // alias even though fills of different slots complete out of order.
     if (warp == NCW) {
-        if (lane == 0 && nrows_c > 0) {
+        if (lane < ns && nrows_c > 0) {
             const uint64_t pol = policy_evict_first();
-            uint32_t slot = 0, phase = 0;
+            const uint32_t Q = (uint32_t)a.n_steps * (uint32_t)nrows_c;  // rows of the launch (host: < 2^31)
+            const uint32_t eb = smem_u32(&empty[lane]), fb = smem_u32(&full[lane]);
+            const uint32_t dstb = smem_u32(ring + (size_t)lane * row_bytes);
+            uint32_t s = (uint32_t)lane / (uint32_t)nrows_c, i = (uint32_t)lane % (uint32_t)nrows_c;
+            uint32_t s_cur = 0, phase = 0;
             long long mb = mb0;
-            for (int s = 0; s < a.n_steps; ++s) {
-                const float* src = nullptr;
-                long long room = 0;  // consecutive positions left in consecutive rows of the same shard
-                for (int i = 0; i < nrows_c; ++i) {
-                    if (room == 0) {
-                        const RowRef ref = locate_row(a, mb, lo + (long long)i * pstride);
-                        src = ref.x;
-                        room = ilv ? 1 : ref.room;
-                    }
-                    mbar_wait(smem_u32(&empty[slot]), phase ^ 1u, a.err);
-                    const uint32_t fb = smem_u32(&full[slot]);
-                    mbar_arrive_expect_tx(fb, (uint32_t)row_bytes);
-                    {
-                        const unsigned char* srcb = reinterpret_cast<const unsigned char*>(src);
-                        const uint32_t dstb = smem_u32(ring + (size_t)slot * row_bytes);
-                        for (uint32_t o = 0; o < (uint32_t)row_bytes; o += (uint32_t)a.tma_chunk) {
-                            const uint32_t m = min((uint32_t)a.tma_chunk, (uint32_t)row_bytes - o);
-                            bulk_g2s(dstb + o, srcb + o, m, fb, pol);
-                        }
-                    }
-                    if (++slot == (uint32_t)ns) { slot = 0; phase ^= 1u; }
-                    src += F;
-                    --room;
+            for (uint32_t q = (uint32_t)lane; q < Q; q += (uint32_t)ns) {
+                while (s_cur < s) { mb = wrap(mb + a.vB); ++s_cur; }
+                const RowRef ref = locate_row(a, mb, lo + (long long)i * pstride);
+                mbar_wait(eb, phase ^ 1u, a.err);
+                mbar_arrive_expect_tx(fb, (uint32_t)row_bytes);
+                const unsigned char* srcb = reinterpret_cast<const unsigned char*>(ref.x);
+                for (uint32_t o = 0; o < (uint32_t)row_bytes; o += (uint32_t)a.tma_chunk) {
+                    const uint32_t m = min((uint32_t)a.tma_chunk, (uint32_t)row_bytes - o);
+                    bulk_g2s(dstb + o, srcb + o, m, fb, pol);
                 }
-                mb = wrap(mb + a.vB);
+                phase ^= 1u;
+                i += (uint32_t)ns;
+                while (i >= (uint32_t)nrows_c) { i -= (uint32_t)nrows_c; ++s; }
             }
         }
         return;

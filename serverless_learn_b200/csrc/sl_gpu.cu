@@ -113,7 +113,7 @@ const Variant kVariants[] = {
     SL_WIDE(10, 14, 1, 2),            // 26: F <= 17920, one group, two rows per pass
 };
 // auto-selection: the first of these that is wide enough for F
-const int kAutoOrder[] = {1, 5, 22, 21, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
+const int kAutoOrder[] = {1, 5, 22, 14, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 }  // namespace
@@ -339,9 +339,12 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
         const size_t fixed_w = red_w + zy_w + gout_w + 512;
         if (h->smem_optin < fixed_w + 16 + (size_t)a.row_bytes) { *why = "row does not fit in shared memory"; return false; }
         size_t nsw = (h->smem_optin - fixed_w) / ((size_t)a.row_bytes + 16);
-        nsw = std::min<size_t>(nsw, 64);
+        nsw = std::min<size_t>(nsw, 32);  // one producer lane per slot
         if (h->opt_ring > 0) nsw = std::min<size_t>(nsw, (size_t)h->opt_ring);
-        if (nsw < (size_t)v.rs) { *why = "ring too short for the rows a group takes per pass"; return false; }
+        // a slot must always be consumed by the same row group (the parity waits on its barriers
+        // cannot tell two rounds apart otherwise): ring length = a multiple of NG*R rows
+        nsw -= nsw % ((size_t)v.r * v.rs);
+        if (nsw < (size_t)v.r * v.rs) { *why = "ring too short for this variant's row groups"; return false; }
         a.ns = (int)nsw;
         size_t offw = (size_t)a.ns * a.row_bytes;
         offw = align_up(offw, 16); a.off_bar = (int)offw;   offw += 8 * (2 * nsw + 3);
