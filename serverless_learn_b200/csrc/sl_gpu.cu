@@ -378,6 +378,10 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     ns = std::min<size_t>(ns, 256);
     if (h->opt_ring > 0) ns = std::min<size_t>(ns, (size_t)h->opt_ring);
     if (ns < 1) { *why = "no ring slot fits"; return false; }
+    {   // with several row groups a slot should always be consumed by the same group (see K1w)
+        const size_t per_round = (size_t)rg * (size_t)(v.r / v.rs);
+        if (rg > 1 && ns >= per_round) ns -= ns % per_round;
+    }
     a.ns = (int)ns;
     size_t off = (size_t)a.ns * slot_b;
     off = align_up(off, 16); a.off_bar = (int)off;   off += 8 * (2 * ns + 3);
