@@ -341,15 +341,23 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                     for (int p = 0; p < a.nranks; ++p)
                         if (p != a.rank) st_vol_v4(a.peer_x[p] + half + (size_t)a.rank * F + ue, pkt);
                     const uint4* inbox = a.peer_x[a.rank] + half;
-                    for (int p = 0; p < a.nranks; ++p) {
-                        if (p == a.rank) continue;
-                        uint4 q = ld_vol_v4(inbox + (size_t)p * F + ue);
+                    for (int p0 = 0; p0 < a.nranks; p0 += 2) {  // two peers' packets in flight at a time
+                        const int p1 = p0 + 1;
+                        const bool u0 = p0 != a.rank, u1 = p1 < a.nranks && p1 != a.rank;
+                        uint4 q0 = make_uint4(0u, xflag, 0u, xflag), q1 = q0;
+                        if (u0) q0 = ld_vol_v4(inbox + (size_t)p0 * F + ue);
+                        if (u1) q1 = ld_vol_v4(inbox + (size_t)p1 * F + ue);
                         uint32_t spins = 0;
-                        while (q.y != xflag || q.w != xflag) {
+                        while (q0.y != xflag || q0.w != xflag) {
                             if (spin_abort(spins, a.err, kErrTimeoutPeer, kPeerSpinLimit)) break;
-                            q = ld_vol_v4(inbox + (size_t)p * F + ue);
+                            q0 = ld_vol_v4(inbox + (size_t)p0 * F + ue);
                         }
-                        tot += (long long)(((unsigned long long)q.z << 32) | (unsigned long long)q.x);
+                        while (q1.y != xflag || q1.w != xflag) {
+                            if (spin_abort(spins, a.err, kErrTimeoutPeer, kPeerSpinLimit)) break;
+                            q1 = ld_vol_v4(inbox + (size_t)p1 * F + ue);
+                        }
+                        tot += (long long)(((unsigned long long)q0.z << 32) | (unsigned long long)q0.x);
+                        tot += (long long)(((unsigned long long)q1.z << 32) | (unsigned long long)q1.x);
                     }
                 }
                 const double m = __ldcg(a.model + ue) - a.eta_over_b * ((double)tot * kFixInv);
