@@ -203,8 +203,11 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-__device__ __forceinline__ float softplus_f(float z) {
-    return fmaxf(z, 0.0f) + log1pf(expf(-fabsf(z)));
+// loss of one row, softplus(z) - y*z, summed so that the large parts cancel exactly first
+// (y in {0,1}: max(z,0) - y*z is 0 or |z| without rounding; adding it to log1p(...) afterwards
+// keeps the small term that softplus(z) - y*z would round away once |z| exceeds ~16)
+__device__ __forceinline__ float row_loss_f(float z, float y) {
+    return (fmaxf(z, 0.0f) - y * z) + log1pf(expf(-fabsf(z)));
 }
 __device__ __forceinline__ float sigmoid_f(float z) { return 1.0f / (1.0f + expf(-z)); }
 
@@ -934,7 +937,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             float l = 0.f;
             for (int i = lane; i < nrows_c; i += 32) {
                 const float2 v = zyb[i];
-                l += softplus_f(v.x) - v.y * v.x;
+                l += row_loss_f(v.x, v.y);
             }
             l = warp_sum(l);
             if (lane == 0) red_add_u64(a.loss_fix + s, (unsigned long long)to_fix(l));
@@ -1001,7 +1004,7 @@ __global__ void __launch_bounds__(256) lr_fwd_kernel(const float* __restrict__ X
     if (lane == 0) {
         const float yy = y[row];
         resid[j] = sigmoid_f(z) - yy;
-        rowloss[j] = softplus_f(z) - yy * z;
+        rowloss[j] = row_loss_f(z, yy);
     }
 }
 

@@ -291,7 +291,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
             float l = 0.f;
             for (int i = lane; i < nrows_c; i += 32) {
                 const float2 v = zyb[i];
-                l += softplus_f(v.x) - v.y * v.x;
+                l += row_loss_f(v.x, v.y);
             }
             l = warp_sum(l);
             if (lane == 0) red_add_u64(a.loss_fix + s, (unsigned long long)to_fix(l));

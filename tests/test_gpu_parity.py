@@ -212,6 +212,14 @@ def test_lr_wide_rows_on_small_grids(sl, orc, variant, F, grid):
     assert ew <= W_TOL and el <= L_TOL, (ew, el, info)
 
 
+@pytest.mark.parametrize("variant,F", [(1, 1024), (5, 2048), (22, 4096), (14, 8192), (11, 16384), (24, 2048)])
+def test_lr_batch_larger_than_shard(sl, orc, variant, F):
+    # B > n_rows: rows repeat inside a minibatch and every step wraps the shard several times
+    ew, el, info, _, _ = _run_case(sl, orc, 37, F, 200, 5, 0.2, 1, variant=variant)
+    assert info[:2] == (1, variant)
+    assert ew <= W_TOL and el <= L_TOL, (ew, el, info)
+
+
 def test_lr_unaligned_F_uses_simple_path(sl, orc):
     ew, el, info, _, _ = _run_case(sl, orc, 333, 77, 50, 9, 0.2, 0)
     assert info[0] == 2
