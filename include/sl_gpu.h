@@ -123,7 +123,10 @@ int sl_shard_synth(sl_handle* h, long long n_rows, unsigned long long row0,
  * sl_train_steps is what takes that slot in this build: n_steps minibatch steps of
  * logistic regression over the resident shard, rows (t*B + j) mod n_rows, t
  * continuing from the previous call (reset by sl_shard_end).  loss_out (nullable)
- * receives n_steps mean losses.  Blocks until the steps are done. */
+ * receives n_steps mean losses.  Blocks until the steps are done.
+ * Range: gradient sums travel as 64-bit fixed point in units of 2^-36, so for every column
+ * |sum over the minibatch (and over all ranks) of (sigmoid(z)-y)*x| must stay below 2^27
+ * (1.3e8) — any fp32 data of ordinary scale; labels may be anywhere in [0,1]. */
 int sl_train_tick(sl_handle* h);
 int sl_train_steps(sl_handle* h, int n_steps, double* loss_out);
 /* Device time (CUDA events on the handle's stream) of the kernels of the last

@@ -220,6 +220,25 @@ def test_lr_batch_larger_than_shard(sl, orc, variant, F):
     assert ew <= W_TOL and el <= L_TOL, (ew, el, info)
 
 
+@pytest.mark.parametrize("path,variant,F", [(1, 1, 256), (1, 22, 4096), (2, 0, 256)])
+def test_lr_soft_labels_and_scaled_features(sl, orc, path, variant, F):
+    # labels anywhere in [0,1] and features of mixed scale (columns scaled 1e-3 .. 30): the step is
+    # defined for any fp32 data whose per-column gradient sum stays inside the fixed-point range
+    n, B, steps, eta = 500, 120, 8, 0.01
+    rng = np.random.default_rng(5)
+    X, _ = orc.synth(0, n, F)
+    X = (X * np.exp(rng.uniform(np.log(1e-3), np.log(30.0), size=F)).astype(np.float32)).astype(np.float32)
+    y = rng.uniform(0.0, 1.0, size=n).astype(np.float32)
+    w = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, steps, w, eta)
+    with sl.Replica(F, B, eta=eta) as r:
+        r.set_option("path", path)
+        r.set_option("variant", variant)
+        r.load_shard(X, y)
+        lg = r.train_steps(steps)
+        assert w_err(r.model(), w) <= W_TOL and float(np.max(np.abs(lg - lo) / np.abs(lo))) <= L_TOL
+
+
 def test_lr_unaligned_F_uses_simple_path(sl, orc):
     ew, el, info, _, _ = _run_case(sl, orc, 333, 77, 50, 9, 0.2, 0)
     assert info[0] == 2
