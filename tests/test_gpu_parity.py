@@ -535,3 +535,51 @@ def test_group_equals_one_worker_when_W_is_1_and_rejects_mismatches(sl, orc):
         c.load_shard(X, y)
         with pytest.raises(sl.SlError):
             sl.Replica.train_steps_group([a, c], 1)          # a is at step 7, c at step 0
+
+
+def test_concurrent_callers_one_handle(sl, orc):
+    # §8(b) threading: the reference's handlers, gossip thread and training thread touch the replica
+    # concurrently with no lock; the library serialises them per handle.  Four threads merge
+    # integer-valued deltas (exact in fp64, so the order cannot show) while a fifth trains and a
+    # sixth streams the next shard in; afterwards the merged part is exactly the sum.
+    import threading
+    F, B, n = 64, 32, 400
+    X, y = orc.synth(0, n, F)
+    with sl.Replica(F, B, eta=0.0) as r:            # eta = 0: training must leave the model alone
+        r.load_shard(X, y)
+        errors = []
+
+        def merger(k):
+            try:
+                for i in range(50):
+                    r.exchange_updates(np.full(F, float(2 * (k + 1))))      # model += 0.5 * 2(k+1)
+            except Exception as ex:                 # noqa: BLE001
+                errors.append(ex)
+
+        def trainer():
+            try:
+                for _ in range(20):
+                    r.train_steps(3)
+            except Exception as ex:                 # noqa: BLE001
+                errors.append(ex)
+
+        def streamer():
+            try:
+                raw = X.tobytes() + y.tobytes()
+                for _ in range(5):
+                    r.shard_begin(len(raw))
+                    for o in range(0, len(raw), 7001):
+                        r.shard_append(raw[o:o + 7001])
+                    r.shard_end()
+            except Exception as ex:                 # noqa: BLE001
+                errors.append(ex)
+
+        ts = [threading.Thread(target=merger, args=(k,)) for k in range(4)]
+        ts += [threading.Thread(target=trainer), threading.Thread(target=streamer)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        assert not errors, errors
+        assert np.array_equal(r.model(), np.full(F, 50.0 * (1 + 2 + 3 + 4)))
+        assert r.info("n_rows") == n
