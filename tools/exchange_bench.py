@@ -1,6 +1,5 @@
 """Exchange arithmetic (a2-a4) as blocking C-ABI calls, us/call (diagnostic): python tools/exchange_bench.py
-sl_merge / sl_delta_snapshot / sl_apply_reply / sl_gossip_p2p / sl_train_tick at D = 1024 and 16384,
-next to the oracle's CPU merge (uses oracle/: lives under tools/ as a measurement script only)."""
+sl_merge / sl_delta_snapshot / sl_apply_reply / sl_gossip_p2p / sl_train_tick at D = 1024 and 16384."""
 import os
 import sys
 import time
@@ -9,12 +8,6 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from serverless_learn_b200 import Replica  # noqa: E402
-
-try:
-    import oracle
-    orc = oracle.Oracle()
-except Exception:  # noqa: BLE001
-    orc = None
 
 
 def timeit(fn, n=2000):
@@ -37,7 +30,4 @@ for D in (1024, 16384):
             "sl_gossip_p2p (whole round, one kernel)": timeit(lambda: a.gossip_p2p(b)),
             "sl_train_tick": timeit(lambda: a.train_tick()),
         }
-        if orc is not None:
-            m, o = d.copy(), np.zeros(D)
-            res["oracle merge on one host core"] = timeit(lambda: orc.merge_callee(m, o, d))
         print(f"D={D}: " + "; ".join(f"{k} {v:.1f} us" for k, v in res.items()), flush=True)
