@@ -231,6 +231,10 @@ class Worker:
     def handle(self):
         return self.L.slr_worker_handle(self.p)
 
+    def replica_shard_synth(self, n_rows: int, row0: int = 0, seed: int = 0x5EED) -> None:
+        """Fill this worker's shard on the device with synthetic rows (benchmarks; sl_shard_synth)."""
+        assert _lib.load().sl_shard_synth(self.handle, n_rows, row0, seed) == 0
+
     def receive_file(self, chunks) -> bool:
         ok = bool(self.L.slr_worker_receive_begin(self.p))
         for ch in chunks:
