@@ -117,6 +117,9 @@ int slr_worker_exchange_updates(slr_worker* w, const double* delta, int n, doubl
 /* W workers of this process that share one GPU take n_steps synchronous steps as one job
  * (sl_train_steps_group: BASELINE config 2, "4 workers ... same 4-shard job on 1 B200").  1 = ok. */
 int slr_workers_train_steps_group(slr_worker* const* ws, int W, int n_steps, double* loss_out);
+/* The same W workers each take n_steps LOCAL steps side by side in one kernel (sl_train_steps_multi):
+ * the bodies of W training threads (src/worker.cc:221-231) in one call.  loss_out: W*n_steps, worker-major. */
+int slr_workers_train_steps_multi(slr_worker* const* ws, int W, int n_steps, double* loss_out);
 int slr_worker_gossip_once(slr_worker* w, slr_directory* d);
 /* one iteration of simulate_training (:221-231) without the sleep: the reference's +1 ... */
 int slr_worker_train_tick(slr_worker* w);

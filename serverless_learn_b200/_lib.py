@@ -44,6 +44,7 @@ _SIGS = {
     "sl_allreduce_avg": (C.c_int, [_h]),
     "sl_train_steps_sync": (C.c_int, [_h, C.c_int, _dp]),
     "sl_train_steps_group": (C.c_int, [C.POINTER(_h), C.c_int, C.c_int, _dp]),
+    "sl_train_steps_multi": (C.c_int, [C.POINTER(_h), C.c_int, C.c_int, _dp]),
     "sl_lr_step_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int,
                                      C.c_longlong, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

@@ -150,6 +150,17 @@ class Replica:
         first._ck(first._L.sl_train_steps_group(arr, len(replicas), n_steps, _d(loss) if want_loss else None))
         return loss[:n_steps] if want_loss else None
 
+    @staticmethod
+    def train_steps_multi(replicas, n_steps: int, want_loss: bool = True):
+        """W replicas sharing one GPU each take n_steps LOCAL steps as one kernel (sl_train_steps_multi);
+        returns the losses as [W, n_steps]."""
+        first = replicas[0]
+        W = len(replicas)
+        arr = (type(first._h) * W)(*[r._h for r in replicas])
+        loss = np.empty(max(n_steps, 1) * W, dtype=np.float64)
+        first._ck(first._L.sl_train_steps_multi(arr, W, n_steps, _d(loss) if want_loss else None))
+        return loss[:n_steps * W].reshape(W, n_steps) if want_loss else None
+
     def last_train_ms(self) -> float:
         return float(self._L.sl_last_train_ms(self._h))
 

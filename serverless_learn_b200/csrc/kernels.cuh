@@ -294,6 +294,12 @@ struct LrArgs {
     int vB;
     const float* vX[8];
     const float* vy[8];
+    // several INDEPENDENT replicas on one GPU, each taking its own local steps (sl_train_steps_multi):
+    // the grid is cut into npart equal partitions of CTAs; partition k trains pmodel[k] on shard
+    // (vX[k], vy[k]) with its own accumulators, counter and loss slots.  npart <= 1: one replica.
+    int npart;
+    int loss_stride;       // loss slots per partition (= steps of the whole call)
+    double* pmodel[8];
 };
 
 // where position p of the current minibatch lives: shard row pointer and label pointer;
@@ -303,9 +309,9 @@ struct RowRef {
     const float* y;
     long long room;
 };
-__device__ __forceinline__ RowRef locate_row(const LrArgs& a, long long mb, long long p) {
-    const float* X = a.X;
-    const float* y = a.y;
+__device__ __forceinline__ RowRef locate_row(const LrArgs& a, long long mb, long long p, int part = 0) {
+    const float* X = a.npart > 1 ? a.vX[part] : a.X;
+    const float* y = a.npart > 1 ? a.vy[part] : a.y;
     long long r = p, lim = a.n_rows;
     if (a.nvw > 1) {
         const int k = (int)(p / a.vB);
@@ -381,7 +387,14 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     constexpr int SPB = R / RS;  // ring slots per sub-batch
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int c = blockIdx.x, G = gridDim.x;
+    // grid partition of this CTA (sl_train_steps_multi): independent replicas, nothing shared
+    const int G = a.npart > 1 ? (int)gridDim.x / a.npart : (int)gridDim.x;
+    const int part = a.npart > 1 ? (int)blockIdx.x / G : 0;
+    const int c = (int)blockIdx.x - part * G;
+    double* const model = a.npart > 1 ? a.pmodel[part] : a.model;
+    unsigned long long* const acc = a.acc + (size_t)part * 3 * (size_t)a.krep * (size_t)a.Fp;
+    unsigned* const counter = a.counter + part * 8;
+    unsigned long long* const loss_fix = a.loss_fix ? a.loss_fix + (size_t)part * a.loss_stride : nullptr;
 
     unsigned char* ring = smem;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.off_bar);    // [ns]
@@ -461,7 +474,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     uint32_t dst = smem_u32(ring + (size_t)slot * slot_bytes);
                     int left = rc;
                     while (left > 0) {  // one copy unless the rows wrap around the shard end (or change worker)
-                        const RowRef ref = locate_row(a, mb, p);
+                        const RowRef ref = locate_row(a, mb, p, part);
                         const int n = ref.room < (long long)left ? (int)ref.room : left;
                         {   // several moderate copies keep more requests in flight than one large one
                             const unsigned char* srcb = reinterpret_cast<const unsigned char*>(ref.x);
@@ -488,7 +501,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     // =========================================================================== exchange
     if (warp == NCW + 1) {
         for (int s = 0; s < a.n_steps; ++s) {
-            unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
+            unsigned long long* buf = acc + (size_t)(s % 3) * acc_stride;
             // the CTA's gradient is staged (XB) or has been added by the compute threads
             mbar_wait(smem_u32(gfull), (uint32_t)s & 1u, a.err);
             if (lane == 0) {
@@ -517,9 +530,9 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     asm volatile("fence.proxy.async;" ::: "memory");
                 }
                 if (XB && a.relaxed_signal)
-                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(a.counter), "r"(1u) : "memory");
+                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(counter), "r"(1u) : "memory");
                 else
-                    red_release_add_u32(a.counter, 1u);
+                    red_release_add_u32(counter, 1u);
                 mbar_arrive(smem_u32(rgo));  // the producer may refill what step s freed
                 dbg_stamp(a, s, 3);
                 const unsigned want = (unsigned)G * (unsigned)(s + 1);
@@ -528,7 +541,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     const long long t0 = clock64();
                     while (clock64() - t0 < a.poll_pause) {}
                 }
-                while ((int)(ld_relaxed_u32(a.counter) - want) < 0) {
+                while ((int)(ld_relaxed_u32(counter) - want) < 0) {
                     if (spin_abort(spins, a.err, kErrTimeoutPart)) break;
                 }
                 asm volatile("fence.acq_rel.gpu;" ::: "memory");
@@ -609,7 +622,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             // Everybody has contributed to step s, hence finished reading the buffer of
             // step s-1: clear this CTA's slice of it for step s+2.  The stores precede this
             // warp's next release on the counter.
-            unsigned long long* z = a.acc + (size_t)((s + 2) % 3) * acc_stride;
+            unsigned long long* z = acc + (size_t)((s + 2) % 3) * acc_stride;
             for (size_t i = (size_t)c * 32 + lane; i < acc_stride; i += (size_t)G * 32) z[i] = 0ull;
             __syncwarp();
         }
@@ -647,7 +660,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             if (WM == 0) { wm[ch][0] = wm[ch][1] = wm[ch][2] = wm[ch][3] = 0.0; }
             continue;
         }
-        const double* m = a.model + gq[ch] * 4;
+        const double* m = model + gq[ch] * 4;
         const float4 wf = make_float4((float)m[0], (float)m[1], (float)m[2], (float)m[3]);
         if (WS) {
             if (rg == 0) {  // one group seeds the CTA's master copy; every group its own smem words
@@ -661,14 +674,14 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         }
     }
     if (MS && tid < granules) {
-        const double* m = a.model + tid * 4;
+        const double* m = model + tid * 4;
         msm[tid * 4 + 0] = m[0]; msm[tid * 4 + 1] = m[1]; msm[tid * 4 + 2] = m[2]; msm[tid * 4 + 3] = m[3];
     }
     if (WS) named_bar_sync(1, NCT);
 
     // apply the exact gradient total of step s to this thread's weights
     auto apply_total = [&](int s) {
-        const unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
+        const unsigned long long* buf = acc + (size_t)(s % 3) * acc_stride;
         if (MS) {
             if (tid < granules) {  // one updater per column chunk; XB is implied by the variant table
                 long long t[4] = {0, 0, 0, 0};
@@ -749,7 +762,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     // label of the row this lane finishes, fetched one stage ahead of its use
     auto load_y = [&](long long mbs, int j) -> float {
         const int i = j * R + ridx;
-        return (active && j < nst_c && i < nrows_c) ? __ldg(locate_row(a, mbs, lo + i).y) : 0.f;
+        return (active && j < nst_c && i < nrows_c) ? __ldg(locate_row(a, mbs, lo + i, part).y) : 0.f;
     };
     float y_next = load_y(mb, rg);
 
@@ -854,7 +867,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             if (ridx < rc) {
                 resid = sigmoid_f(z) - yv;
                 // the loss is evaluated after the gradient has been handed off
-                if (canon && wig == 0 && a.loss_fix) zyb[j * R + ridx] = make_float2(z, yv);
+                if (canon && wig == 0 && loss_fix) zyb[j * R + ridx] = make_float2(z, yv);
             }
 #pragma unroll
             for (int r = 0; r < R; ++r) {
@@ -890,7 +903,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             named_bar_sync(1, NCT);
         }
         if (comb) {
-            unsigned long long* buf = a.acc + (size_t)(s % 3) * acc_stride;
+            unsigned long long* buf = acc + (size_t)(s % 3) * acc_stride;
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch) {
                 int gqc;
@@ -933,14 +946,14 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         }
         if (tid == 0) dbg_stamp(a, s, 2);
         // off the critical path (the exchange is in flight): this step's loss
-        if (warp == 0 && a.loss_fix) {
+        if (warp == 0 && loss_fix) {
             float l = 0.f;
             for (int i = lane; i < nrows_c; i += 32) {
                 const float2 v = zyb[i];
                 l += row_loss_f(v.x, v.y);
             }
             l = warp_sum(l);
-            if (lane == 0) red_add_u64(a.loss_fix + s, (unsigned long long)to_fix(l));
+            if (lane == 0) red_add_u64(loss_fix + s, (unsigned long long)to_fix(l));
         }
         mb = mb_next;
     }
@@ -953,14 +966,14 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     // master weights back to global: all CTAs hold identical copies, CTA 0 writes
     if (MS) {
         if (c == 0 && tid < granules) {
-            double* m = a.model + tid * 4;
+            double* m = model + tid * 4;
             m[0] = msm[tid * 4]; m[1] = msm[tid * 4 + 1]; m[2] = msm[tid * 4 + 2]; m[3] = msm[tid * 4 + 3];
         }
     } else if (c == 0 && rg == 0) {
 #pragma unroll
         for (int ch = 0; ch < CH; ++ch) {
             if (!gv[ch]) continue;
-            double* m = a.model + gq[ch] * 4;
+            double* m = model + gq[ch] * 4;
             if (WS) {
                 const double* mm = my_master + gq[ch] * 4;
                 m[0] = mm[0]; m[1] = mm[1]; m[2] = mm[2]; m[3] = mm[3];

@@ -460,4 +460,13 @@ int slr_workers_train_steps_group(slr_worker* const* ws, int W, int n_steps, dou
     }
     return sl_train_steps_group(hs, W, n_steps, loss_out) == 0 ? 1 : 0;
 }
+int slr_workers_train_steps_multi(slr_worker* const* ws, int W, int n_steps, double* loss_out) {
+    if (!ws || W < 1 || W > 8) return 0;
+    sl_handle* hs[8];
+    for (int k = 0; k < W; ++k) {
+        if (!ws[k]) return 0;
+        hs[k] = ws[k]->core.handle();
+    }
+    return sl_train_steps_multi(hs, W, n_steps, loss_out) == 0 ? 1 : 0;
+}
 }  // extern "C"

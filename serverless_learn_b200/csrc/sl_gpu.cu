@@ -137,6 +137,8 @@ struct sl_handle {
     // shard
     unsigned char* shard = nullptr;
     size_t shard_cap = 0, shard_len = 0;
+    int npart = 0;                       // >1 while sl_train_steps_multi runs: independent replicas, one grid partition each
+    double* pmodel[8] = {};
     int vw = 0;                          // >1 while sl_train_steps_group runs: worker replicas trained as one job
     const float* vX[8] = {};
     const float* vy[8] = {};
@@ -316,6 +318,12 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     const Variant& v = kVariants[vi];
     int grid = h->num_sms;
     if (h->opt_grid > 0) grid = (int)std::min<long long>(h->opt_grid, h->num_sms);
+    const int npart = h->npart > 1 ? h->npart : 1;
+    if (npart > 1) {
+        if (v.kind != 0 || v.ws != 0 || !v.xb) { *why = "replica partitions run on the register-row kernel only (F <= 2048)"; return false; }
+        grid = grid / npart;  // CTAs per partition; the launch has npart of them
+        if (grid < 1) { *why = "fewer SMs than replicas"; return false; }
+    }
     slk::LrArgs& a = p->args;
     memset(&a, 0, sizeof(a));
     a.F = F;
@@ -323,6 +331,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     a.B = (int)Beff;
     a.vB = h->B;
     a.nvw = h->vw > 1 ? h->vw : 0;
+    a.npart = npart > 1 ? npart : 0;
     a.Fp = F;
     a.zy_rows = (int)((((Beff + grid - 1) / grid + v.r - 1) / v.r) * v.r);
     a.krep = !v.xb ? 1 : (F <= 1024 ? 4 : (F <= 2048 ? 2 : 1));
@@ -394,14 +403,14 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     off = align_up(off, 16); a.off_msm = (int)off;   off += msm_b;
     p->smem = off;
     p->variant = vi;
-    p->grid = grid;
+    p->grid = grid * npart;  // geometry above is per partition
     return true;
 }
 
 int ensure_exchange(sl_handle* h, const PersistPlan& plan) {
     const Variant& v = kVariants[plan.variant];
     const size_t need = v.kind == 1 ? 4 * (size_t)plan.grid * v.r * plan.args.Fp   // K1w: one fp32 partial vector per row group
-                                    : 8 * (size_t)3 * plan.args.krep * plan.args.Fp;
+                                    : 8 * (size_t)3 * plan.args.krep * plan.args.Fp * (plan.args.npart > 1 ? plan.args.npart : 1);
     if (h->acc_bytes < need) {
         if (h->acc) cudaFree(h->acc);
         h->acc = nullptr;
@@ -456,7 +465,8 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
     }
     int done = 0;
     *h->h_err = 0;
-    if (want_loss) CK(h, cudaMemsetAsync(h->loss_fix, 0, 8 * (size_t)n_steps, h->stream));
+    const int np = plan.args.npart > 1 ? plan.args.npart : 1;
+    if (want_loss) CK(h, cudaMemsetAsync(h->loss_fix, 0, 8 * (size_t)n_steps * np, h->stream));
     while (done < n_steps) {
         const int n = std::min(max_per_launch, n_steps - done);
         slk::LrArgs a = plan.args;
@@ -477,10 +487,11 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         a.loss_fix = want_loss ? h->loss_fix + done : nullptr;
         // accumulators and the arrival counter start every launch at zero
         if (kVariants[plan.variant].kind == 0)
-            CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp, h->stream));
-        CK(h, cudaMemsetAsync(h->counter, 0, 128, h->stream));
+            CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp * np, h->stream));
+        CK(h, cudaMemsetAsync(h->counter, 0, 256, h->stream));
         a.eta_over_b = h->eta / (double)a.B;
-        for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; }
+        for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; a.pmodel[k] = h->pmodel[k]; }
+        a.loss_stride = n_steps;
         a.hold_refills = h->opt_hold != 0 ? 1 : 0;
         a.rotate_reduce = h->opt_rotate != 0 ? 1 : 0;
         a.poll_pause = (int)h->opt_poll_pause;
@@ -524,8 +535,8 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         done += n;
     }
     if (want_loss) {
-        slk::loss_finish_kernel<<<(n_steps + 255) / 256, 256, 0, h->stream>>>(
-            h->loss_fix, h->d_loss, n_steps, 1.0 / (double)plan.args.B);
+        slk::loss_finish_kernel<<<(n_steps * np + 255) / 256, 256, 0, h->stream>>>(
+            h->loss_fix, h->d_loss, n_steps * np, 1.0 / (double)plan.args.B);
         h->launches++;
         CK(h, cudaGetLastError());
     }
@@ -580,7 +591,8 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
         return fail(h, SL_ESTATE, "the NCCL path needs sl_comm_init_rank");
     if (n_steps == 0) return SL_OK;
     DeviceGuard dg(h->device);
-    int rc = ensure_loss_cap(h, (size_t)n_steps);
+    const size_t nloss = (size_t)n_steps * (h->npart > 1 ? h->npart : 1);  // one loss per step and replica
+    int rc = ensure_loss_cap(h, nloss);
     if (rc) return rc;
     PersistPlan plan;
     std::string why;
@@ -617,7 +629,7 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     }
     CK(h, cudaEventRecord(h->ev1, h->stream));
     if (loss_out)
-        CK(h, cudaMemcpyAsync(h->h_loss, h->d_loss, sizeof(double) * n_steps, cudaMemcpyDeviceToHost,
+        CK(h, cudaMemcpyAsync(h->h_loss, h->d_loss, sizeof(double) * nloss, cudaMemcpyDeviceToHost,
                               h->stream));
     CK(h, cudaStreamSynchronize(h->stream));
     CK(h, cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
@@ -626,7 +638,7 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
         *h->h_err = 0;
         return fail(h, SL_ETIMEOUT, "in-kernel wait timed out (watchdog code %d)", code);
     }
-    if (loss_out) memcpy(loss_out, h->h_loss, sizeof(double) * n_steps);
+    if (loss_out) memcpy(loss_out, h->h_loss, sizeof(double) * nloss);
     return SL_OK;
 }
 
@@ -1031,6 +1043,50 @@ int sl_train_steps_group(sl_handle* const* handles, int W, int n_steps, double* 
         handles[k]->step = h->step;
     }
     CK(h, cudaStreamSynchronize(h->stream));
+    return SL_OK;
+}
+
+int sl_train_steps_multi(sl_handle* const* handles, int W, int n_steps, double* loss_out) {
+    if (!handles || W < 1 || W > 8) return fail(nullptr, SL_EINVAL, "W must be 1..8");
+    for (int k = 0; k < W; ++k) {
+        if (!handles[k]) return fail(nullptr, SL_EINVAL, "handle %d is NULL", k);
+        for (int j = 0; j < k; ++j)
+            if (handles[j] == handles[k]) return fail(handles[0], SL_EINVAL, "handle %d is listed twice", k);
+    }
+    sl_handle* h = handles[0];
+    std::vector<sl_handle*> order(handles, handles + W);
+    std::sort(order.begin(), order.end());
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (sl_handle* o : order) locks.emplace_back(o->mu);
+    for (int k = 0; k < W; ++k) {
+        sl_handle* w = handles[k];
+        if (w->device != h->device || w->F != h->F || w->B != h->B || w->eta != h->eta)
+            return fail(h, SL_EINVAL, "worker %d differs from worker 0 in device, F, B or eta", k);
+        if (!w->shard_sealed || w->n_rows <= 0) return fail(h, SL_ESTATE, "worker %d has no sealed shard", k);
+        if (w->n_rows != h->n_rows)
+            return fail(h, SL_EINVAL, "worker %d holds %lld rows, worker 0 holds %lld: shards must be equal",
+                        k, w->n_rows, h->n_rows);
+        if (w->step != h->step) return fail(h, SL_ESTATE, "worker %d is at step %lld, worker 0 at %lld", k, w->step, h->step);
+        if (((uintptr_t)(w->shard + w->shard_off) & 15) != 0) return fail(h, SL_EINVAL, "worker %d: shard not 16-byte aligned", k);
+    }
+    if (n_steps < 0) return fail(h, SL_EINVAL, "n_steps < 0");
+    if (n_steps == 0) return SL_OK;
+    DeviceGuard dg(h->device);
+    for (int k = 1; k < W; ++k) CK(h, cudaStreamSynchronize(handles[k]->stream));
+    for (int k = 0; k < W; ++k) {
+        h->vX[k] = reinterpret_cast<const float*>(handles[k]->shard + handles[k]->shard_off);
+        h->vy[k] = h->vX[k] + (size_t)handles[k]->n_rows * h->F;
+        h->pmodel[k] = handles[k]->model;
+    }
+    h->npart = W;
+    const long long saved_path = h->opt_path;
+    if (h->opt_path == 0) h->opt_path = 1;
+    int rc = h->opt_path == 1 ? train_impl(h, n_steps, loss_out, false)
+                              : fail(h, SL_EINVAL, "sl_train_steps_multi runs on the persistent kernel only");
+    h->opt_path = saved_path;
+    h->npart = 0;
+    if (rc) return rc;
+    for (int k = 1; k < W; ++k) handles[k]->step = h->step;
     return SL_OK;
 }
 

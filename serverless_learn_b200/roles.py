@@ -44,6 +44,7 @@ _SIGS = {
     "slr_master_request_pushes": (C.c_int, [_p, _p, _p]),
     "slr_master_do_checkups": (C.c_int, [_p, _p, _p]),
     "slr_workers_train_steps_group": (C.c_int, [C.POINTER(_p), C.c_int, C.c_int, _dp]),
+    "slr_workers_train_steps_multi": (C.c_int, [C.POINTER(_p), C.c_int, C.c_int, _dp]),
     "slr_master_enable_elastic": (C.c_int, [_p, C.c_int]),
     "slr_master_admit_pending": (C.c_int, [_p, _p, _p]),
     "slr_master_gossip_once": (C.c_int, [_p, _p]),
@@ -217,6 +218,16 @@ def train_steps_group(workers, n: int):
     loss = np.empty(max(n, 1))
     assert L.slr_workers_train_steps_group(arr, len(workers), n, _d(loss)) == 1
     return loss[:n]
+
+
+def train_steps_multi(workers, n: int):
+    """W workers sharing one GPU each take n LOCAL steps side by side in one kernel; losses [W, n]."""
+    L = load()
+    W = len(workers)
+    arr = (_p * W)(*[w.p for w in workers])
+    loss = np.empty(max(n, 1) * W)
+    assert L.slr_workers_train_steps_multi(arr, W, n, _d(loss)) == 1
+    return loss[:n * W].reshape(W, n)
 
 
 class Worker:

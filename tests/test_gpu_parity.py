@@ -583,3 +583,44 @@ def test_concurrent_callers_one_handle(sl, orc):
         assert not errors, errors
         assert np.array_equal(r.model(), np.full(F, 50.0 * (1 + 2 + 3 + 4)))
         assert r.info("n_rows") == n
+
+
+# ------------------------------------------------------------------ W independent replicas on one GPU
+@pytest.mark.parametrize("W,n,F,B,variant", [(4, 640, 64, 48, 0), (4, 1200, 1024, 256, 1), (3, 500, 260, 100, 0),
+                                             (8, 96, 16, 7, 0), (2, 700, 2048, 300, 5), (5, 400, 128, 64, 2)])
+def test_multi_replicas_on_one_gpu_take_local_steps(sl, orc, W, n, F, B, variant):
+    # sl_train_steps_multi: the SMs are cut into W partitions, worker k trains its own model on its own
+    # shard; every worker must equal (a) the oracle on its shard and (b), bit for bit, the same worker
+    # training alone on a grid of SMs/W CTAs
+    steps, eta = 9, 0.2
+    shards = [orc.synth(k * n, n, F) for k in range(W)]
+    reps = [sl.Replica(F, B, eta=eta) for _ in range(W)]
+    try:
+        for r, (X, y) in zip(reps, shards):
+            r.load_shard(X, y)
+        reps[0].set_option("variant", variant)
+        lg = np.concatenate([sl.Replica.train_steps_multi(reps, 4), sl.Replica.train_steps_multi(reps, steps - 4)], axis=1)
+        grid = reps[0].info("grid") // W
+        assert reps[0].info("path") == 1 and grid >= 1
+        for k, r in enumerate(reps):
+            ref = np.zeros(F)
+            lo = orc.lr_steps(*shards[k], B, 0, steps, ref, eta)
+            assert w_err(r.model(), ref) <= W_TOL and np.max(np.abs(lg[k] - lo) / lo) <= L_TOL, k
+            assert r.info("step") == steps
+            with sl.Replica(F, B, eta=eta) as solo:
+                solo.load_shard(*shards[k])
+                solo.set_option("variant", variant)
+                solo.set_option("grid", grid)
+                ls = solo.train_steps(steps)
+                assert np.array_equal(solo.model(), r.model()) and np.array_equal(ls, lg[k]), k
+    finally:
+        for r in reps:
+            r.close()
+
+
+def test_multi_rejects_wide_rows(sl, orc):
+    X, y = orc.synth(0, 64, 4096)
+    with sl.Replica(4096, 32) as a, sl.Replica(4096, 32) as b:
+        a.load_shard(X, y); b.load_shard(X, y)
+        with pytest.raises(sl.SlError):
+            sl.Replica.train_steps_multi([a, b], 1)

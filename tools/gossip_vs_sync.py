@@ -1,6 +1,7 @@
 """The reference's asynchronous gossip (§8f n3) next to the synchronous extension, same data, one GPU
 (diagnostic): python tools/gossip_vs_sync.py
-W workers hold their own shards.  Async: every round each worker trains K local steps, then gossips once
+W workers hold their own shards.  Async: every round each worker trains K local steps (all workers side by side in one kernel,
+sl_train_steps_multi), then gossips once
 with a rand()%N partner from its CheckUp peer list (one-kernel P2P round).  Sync: the W workers take the
 same number of steps as one job (sl_train_steps_group).  Prints the mean training loss along the way."""
 import os
@@ -36,7 +37,7 @@ rows = []
 d, fs, master, ws = make()
 t0 = time.perf_counter()
 for rnd in range(ROUNDS):
-    losses = [w.train_steps(K)[-1] for w in ws]
+    losses = roles.train_steps_multi(ws, K)[:, -1]   # the four training threads' K steps, one kernel
     for w in ws:
         w.gossip_once(d)
     if (rnd + 1) % 8 == 0:
