@@ -302,3 +302,39 @@ def test_config2_four_workers_on_one_gpu(orc):
     for w in ws:
         w.close()
     master.close(); fs.close(); d.close()
+
+
+def test_workers_local_steps_side_by_side(orc):
+    # the W training threads' bodies (src/worker.cc:221-231) as one call: every worker takes local steps
+    # on its own shard, then a gossip round couples them — all against the oracle
+    from serverless_learn_b200 import roles
+    F, B, n, W, K = 128, 64, 512, 4, 6
+    d, fs, master = roles.Directory(), roles.FileServer(), roles.Master(F)
+    ws = [roles.Worker(f"w{k}:1", F, B, eta=0.2) for k in range(W)]
+    for k, w in enumerate(ws):
+        d.add(w)
+        master.register_birth(w.addr)
+        assert fs.add_synthetic_shard(k + 1, k * n, n, F)
+    assert master.request_pushes_sharded(fs, d) == W and master.do_checkups(fs, d) == W
+    shards = [orc.synth(k * n, n, F) for k in range(W)]
+    om = [np.zeros(F) for _ in range(W)]
+    oo = [np.zeros(F) for _ in range(W)]
+    libc = C.CDLL("libc.so.6")
+    libc.srand(99)
+    draws = [libc.rand() for _ in range(2 * W)]
+    libc.srand(99)
+    it = iter(draws)
+    for rnd in range(2):
+        lg = roles.train_steps_multi(ws, K)
+        for k in range(W):
+            lo = orc.lr_steps(*shards[k], B, rnd * K, K, om[k], 0.2)
+            assert np.max(np.abs(lg[k] - lo) / lo) <= 1e-5
+        for k, w in enumerate(ws):
+            j = w.gossip_once(d)
+            assert j == next(it) % W
+            reply = orc.merge_callee(om[j], oo[j], orc.delta(om[k], oo[k]))
+            orc.apply_reply(om[k], oo[k], reply)
+    for k, w in enumerate(ws):
+        assert np.max(np.abs(w.model() - om[k])) / np.max(np.abs(om[k])) <= 1e-5
+        w.close()
+    master.close(); fs.close(); d.close()
