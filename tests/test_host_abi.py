@@ -122,3 +122,23 @@ def test_file_server_synthetic_shards(libs, orc):
     d = roles.Directory()
     assert fs.do_push(d, "nobody:1", 2) == -1 and fs.do_push(d, "nobody:1", 3) == 0
     fs.close(); d.close()
+
+
+def test_file_server_described_shard_header(libs, orc):
+    # §8f n2: the 64-byte sl_shard_header (include/sl_gpu.h) in front of the payload
+    import struct
+    from serverless_learn_b200 import roles
+    fs = roles.FileServer()
+    assert fs.add_described_shard(5, 777, 300, 64)
+    n = fs.file_length_of(5)
+    assert n == 64 + 300 * 65 * 4
+    stream = np.concatenate([fs.chunk_of(5, k) for k in range(1)])
+    assert stream.size == n
+    magic, version, F, n_rows, row0, flags, _r0, bsum, wsum, _r1 = struct.unpack("<8sIIQQIIQQQ", stream[:64].tobytes())
+    assert (magic, version, F, n_rows, row0, flags) == (b"SLSHARD\x01", 1, 64, 300, 777, 1)
+    payload = stream[64:]
+    assert bsum == orc.bytesum(payload) and wsum == orc.weighted_sum(payload)
+    X, y = orc.synth(777, 300, 64)
+    raw = payload.view(np.float32)
+    assert np.array_equal(raw[:300 * 64].reshape(300, 64), X) and np.array_equal(raw[300 * 64:], y)
+    fs.close()
