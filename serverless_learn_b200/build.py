@@ -5,6 +5,7 @@
 Outputs (git-ignored, but shipped to the GPU box with the tree):
     serverless_learn_b200/libsl_gpu.so     CUDA kernels + the C ABI of include/sl_gpu.h
     serverless_learn_b200/libsl_roles.so   host-side role cores (include/sl_roles.h)
+    serverless_learn_b200/sl_job           example program: the three roles in one C++ process
 """
 from __future__ import annotations
 
@@ -28,6 +29,11 @@ TARGETS = {
                                  "../../include/sl_gpu.h"],
         cmd=lambda out, srcs: ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-o", out,
                                *srcs, "-L" + HERE, "-lsl_gpu", "-Wl,-rpath,$ORIGIN", "-lpthread"]),
+    # example program: the three roles in one C++ process (examples/sl_job.cc)
+    "sl_job": dict(
+        srcs=["../../examples/sl_job.cc"], deps=["roles.h", "../../include/sl_roles.h", "../../include/sl_gpu.h"],
+        cmd=lambda out, srcs: ["g++", "-O2", "-std=c++17", "-Wall", "-o", out, *srcs, "-L" + HERE, "-lsl_roles",
+                               "-lsl_gpu", "-Wl,-rpath,$ORIGIN", "-lpthread"]),
 }
 
 

@@ -3,6 +3,7 @@ whole in-process job — registration, check-ups, file push, training ticks, gos
 with the master — and every replica is compared with an oracle simulation of the same
 deterministic schedule (repair R8: one schedule instead of racing threads)."""
 import ctypes as C
+import os
 import subprocess
 import sys
 
@@ -338,3 +339,45 @@ def test_workers_local_steps_side_by_side(orc):
         assert np.max(np.abs(w.model() - om[k])) / np.max(np.abs(om[k])) <= 1e-5
         w.close()
     master.close(); fs.close(); d.close()
+
+
+@pytest.mark.parametrize("mode", ["async", "sync"])
+def test_cpp_job_program_matches_the_oracle(orc, mode):
+    # examples/sl_job.cc: the three roles in ONE C++ process (no Python in the loop) — file server, master
+    # (RegisterBirth, sharded DoPush -> ReceiveFile with the self-describing header, CheckUp), W workers that
+    # take local steps side by side and gossip with rand()%N partners (or train synchronously)
+    import json
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "serverless_learn_b200", "sl_job")
+    if not os.path.exists(exe):
+        pytest.skip("sl_job not built")
+    W, n, F, B, R, K, eta = 3, 600, 128, 64, 4, 5, 0.2
+    out = subprocess.run([exe, "--workers", str(W), "--rows", str(n), "--features", str(F), "--batch", str(B),
+                          "--rounds", str(R), "--local-steps", str(K), "--eta", str(eta), "--mode", mode],
+                         capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    got = json.loads(out.stdout.strip().splitlines()[-1])
+    shards = [orc.synth(k * n, n, F) for k in range(W)]
+    if mode == "sync":
+        w = np.zeros(F)
+        lo = orc.lr_steps_sync([s[0] for s in shards], [s[1] for s in shards], B, 0, R * K, w, eta)
+        want = [lo[(r + 1) * K - 1] for r in range(R)]
+        w00 = w[0]
+    else:
+        om = [np.zeros(F) for _ in range(W)]
+        oo = [np.zeros(F) for _ in range(W)]
+        libc = C.CDLL("libc.so.6")
+        libc.srand(1)                                   # the program never seeds rand(): glibc's default
+        want = []
+        for r in range(R):
+            last = []
+            for k in range(W):
+                last.append(orc.lr_steps(*shards[k], B, r * K, K, om[k], eta)[-1])
+            want.append(float(np.mean(last)))
+            for k in range(W):
+                j = libc.rand() % W
+                reply = orc.merge_callee(om[j], oo[j], orc.delta(om[k], oo[k]))
+                orc.apply_reply(om[k], oo[k], reply)
+        w00 = om[0][0]
+    assert np.max(np.abs(np.array(got["mean_loss"]) - np.array(want)) / np.array(want)) <= 1e-5
+    assert abs(got["w0_0"] - w00) <= 1e-5 * abs(w00)

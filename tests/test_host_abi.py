@@ -142,3 +142,19 @@ def test_file_server_described_shard_header(libs, orc):
     raw = payload.view(np.float32)
     assert np.array_equal(raw[:300 * 64].reshape(300, 64), X) and np.array_equal(raw[300 * 64:], y)
     fs.close()
+
+
+def test_cpp_job_program_fails_loudly_without_a_gpu(libs):
+    # examples/sl_job.cc is built by build(); with no CUDA device it must stop with the library's message
+    import subprocess
+    exe = os.path.join(ROOT, "serverless_learn_b200", "sl_job")
+    assert os.path.exists(exe), "build() did not produce sl_job"
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("a GPU is present")
+    except ImportError:
+        pass
+    out = subprocess.run([exe, "--workers", "2", "--rows", "64", "--features", "16", "--batch", "8"],
+                         capture_output=True, text=True, timeout=120)
+    assert out.returncode == 1 and "no CUDA device" in out.stderr, (out.returncode, out.stderr)
