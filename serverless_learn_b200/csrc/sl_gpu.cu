@@ -18,6 +18,7 @@
 
 #include "kernels.cuh"
 #include "kernels_wide.cuh"
+#include "kernels_multi.cuh"
 
 namespace {
 
@@ -170,7 +171,7 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0, opt_persist_l2 = 0, opt_poll_pause = 0, opt_dbg_skip = 0, opt_tma_chunk = 0, opt_relaxed_signal = 0, opt_block_rows = 0;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0, opt_persist_l2 = 0, opt_poll_pause = 0, opt_dbg_skip = 0, opt_tma_chunk = 0, opt_relaxed_signal = 0, opt_block_rows = 0, opt_multi_mode = 0, opt_multi_lpw = 0;
     bool l2_window_set = false;
     unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
@@ -581,6 +582,100 @@ int launch_simple_step(sl_handle* h, double* d_loss_slot, bool sync) {
     return SL_OK;
 }
 
+// K1m: NM <= 4 independent replicas interleaved on every SM (kernels_multi.cuh).  F <= 1024.
+constexpr int kIlvR = 16, kIlvRS = 4, kIlvNCW = 8;
+bool interleaved_ok(const sl_handle* h) {
+    return h->npart >= 2 && h->npart <= 4 && h->F % 4 == 0 && h->F <= 4 * 32 * kIlvNCW && h->coop &&
+           h->opt_multi_mode == 0 && h->opt_variant == 0;
+}
+int run_interleaved(sl_handle* h, int n_steps, bool want_loss) {
+    const int NM = h->npart, F = h->F;
+    // exchange lanes per warp: 1 = a warp per model (experiment knob "multi_lpw")
+    const int lpw = h->opt_multi_lpw > 0 ? (int)std::min<long long>(h->opt_multi_lpw, NM) : (NM == 4 ? 2 : 1);
+    const void* fn = nullptr;
+#define SL_ILV(N, L) if (NM == N && lpw == L) fn = (const void*)slk::lr_interleaved_kernel<kIlvR, kIlvRS, kIlvNCW, N, L>;
+    SL_ILV(2, 1) SL_ILV(2, 2) SL_ILV(3, 1) SL_ILV(3, 3) SL_ILV(4, 1) SL_ILV(4, 2) SL_ILV(4, 4)
+#undef SL_ILV
+    if (!fn) return fail(h, SL_EINVAL, "no interleaved kernel for %d replicas with %d exchange lanes per warp", NM, lpw);
+    const int xwarps = (NM + lpw - 1) / lpw;
+    int grid = h->num_sms;
+    if (h->opt_grid > 0) grid = (int)std::min<long long>(h->opt_grid, h->num_sms);
+    slk::LrArgs a;
+    memset(&a, 0, sizeof(a));
+    a.F = F; a.Fp = F; a.B = h->B; a.vB = h->B; a.n_rows = h->n_rows; a.npart = NM; a.krep = 1;
+    a.row_bytes = 4 * F;
+    a.zy_rows = (int)((((long long)h->B + grid - 1) / grid + kIlvR - 1) / kIlvR * kIlvR);
+    const size_t red_b = sizeof(float) * 2 * kIlvNCW * kIlvR;
+    const size_t zy_b = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
+    const size_t vec_b = 8 * (size_t)F * NM;  // gout, gin, masters: one of each per model
+    const size_t fixed = red_b + zy_b + 3 * vec_b + 1024;
+    const size_t slot_b = (size_t)kIlvRS * a.row_bytes;
+    if (h->smem_optin < fixed + (slot_b + 16) * (kIlvR / kIlvRS))
+        return fail(h, SL_EINVAL, "the interleaved kernel does not fit in shared memory at F = %d", F);
+    size_t ns = std::min<size_t>((h->smem_optin - fixed) / (slot_b + 16), 32);  // one producer lane per slot
+    if (h->opt_ring > 0) ns = std::max<size_t>(kIlvR / kIlvRS, std::min<size_t>(ns, (size_t)h->opt_ring));
+    a.ns = (int)ns;
+    size_t off = ns * slot_b;
+    off = align_up(off, 16); a.off_bar = (int)off;   off += 8 * (2 * ns + 2 * NM);
+    off = align_up(off, 16); a.off_red = (int)off;   off += red_b;
+    off = align_up(off, 16); a.off_zy = (int)off;    off += zy_b;
+    off = align_up(off, 128); a.off_gout = (int)off; off += vec_b;
+    off = align_up(off, 128); a.off_gin = (int)off;  off += vec_b;
+    off = align_up(off, 16); a.off_msm = (int)off;   off += vec_b;
+    const size_t smem = off;
+    const size_t need = 8 * (size_t)3 * F * NM;
+    if (h->acc_bytes < need) {
+        if (h->acc) cudaFree(h->acc);
+        h->acc = nullptr;
+        h->acc_bytes = 0;
+        CK(h, cudaMalloc(&h->acc, need));
+        h->acc_bytes = need;
+    }
+    if (!h->counter) CK(h, cudaMalloc(&h->counter, 256));
+    CK(h, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    const int threads = (kIlvNCW + 1 + xwarps) * 32;
+    CK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, threads, smem));
+    if (occ < 1) return fail(h, SL_ECUDA, "interleaved kernel does not fit on an SM");
+    const int max_per_launch = h->opt_steps_per_launch > 0 ? (int)h->opt_steps_per_launch : kMaxStepsPerLaunch;
+    *h->h_err = 0;
+    if (want_loss) CK(h, cudaMemsetAsync(h->loss_fix, 0, 8 * (size_t)n_steps * NM, h->stream));
+    int done = 0;
+    while (done < n_steps) {
+        const int n = std::min(max_per_launch, n_steps - done);
+        a.step0 = h->step;
+        a.n_steps = n;
+        a.acc = h->acc;
+        a.counter = h->counter;
+        a.loss_fix = want_loss ? h->loss_fix + done : nullptr;
+        a.loss_stride = n_steps;
+        a.eta_over_b = h->eta / (double)h->B;
+        a.err = h->d_err;
+        a.tma_chunk = 1 << 20;
+        for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; a.pmodel[k] = h->pmodel[k]; }
+        CK(h, cudaMemsetAsync(h->acc, 0, need, h->stream));
+        CK(h, cudaMemsetAsync(h->counter, 0, 256, h->stream));
+        void* params[] = {&a};
+        CK(h, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(threads), params, smem, h->stream));
+        h->launches++;
+        h->k1_launches++;
+        h->step += n;
+        done += n;
+    }
+    if (want_loss) {
+        slk::loss_finish_kernel<<<(n_steps * NM + 255) / 256, 256, 0, h->stream>>>(
+            h->loss_fix, h->d_loss, n_steps * NM, 1.0 / (double)h->B);
+        h->launches++;
+        CK(h, cudaGetLastError());
+    }
+    h->path_used = 5;
+    h->variant_used = 0;
+    h->grid_used = grid;
+    h->ns_used = a.ns;
+    h->smem_used = (long long)smem;
+    return SL_OK;
+}
+
 int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     if (n_steps < 0) return fail(h, SL_EINVAL, "n_steps < 0");
     if (!h->shard_sealed || h->n_rows <= 0)
@@ -594,6 +689,23 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     const size_t nloss = (size_t)n_steps * (h->npart > 1 ? h->npart : 1);  // one loss per step and replica
     int rc = ensure_loss_cap(h, nloss);
     if (rc) return rc;
+    if (!sync && interleaved_ok(h)) {  // independent replicas, interleaved on every SM
+        CK(h, cudaEventRecord(h->ev0, h->stream));
+        rc = run_interleaved(h, n_steps, loss_out != nullptr);
+        if (rc) return rc;
+        CK(h, cudaEventRecord(h->ev1, h->stream));
+        if (loss_out)
+            CK(h, cudaMemcpyAsync(h->h_loss, h->d_loss, sizeof(double) * nloss, cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+        CK(h, cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
+        if (*h->h_err != 0) {
+            const int code = *h->h_err;
+            *h->h_err = 0;
+            return fail(h, SL_ETIMEOUT, "in-kernel wait timed out (watchdog code %d)", code);
+        }
+        if (loss_out) memcpy(loss_out, h->h_loss, sizeof(double) * nloss);
+        return SL_OK;
+    }
     PersistPlan plan;
     std::string why;
     bool persist = !sync && h->opt_path != 2 && plan_persist(h, &plan, &why);
@@ -763,6 +875,8 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "persist_l2") h->opt_persist_l2 = value;
     else if (k == "relaxed_signal") h->opt_relaxed_signal = value;
     else if (k == "block_rows") h->opt_block_rows = value;
+    else if (k == "multi_mode") h->opt_multi_mode = value;
+    else if (k == "multi_lpw") h->opt_multi_lpw = value;
     else if (k == "poll_pause") h->opt_poll_pause = value;
     else if (k == "debug_skip_compute") h->opt_dbg_skip = value;
     else if (k == "tma_chunk") h->opt_tma_chunk = value;

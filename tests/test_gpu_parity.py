@@ -587,7 +587,8 @@ def test_concurrent_callers_one_handle(sl, orc):
 
 # ------------------------------------------------------------------ W independent replicas on one GPU
 @pytest.mark.parametrize("W,n,F,B,variant", [(4, 640, 64, 48, 0), (4, 1200, 1024, 256, 1), (3, 500, 260, 100, 0),
-                                             (8, 96, 16, 7, 0), (2, 700, 2048, 300, 5), (5, 400, 128, 64, 2)])
+                                             (8, 96, 16, 7, 0), (2, 700, 2048, 300, 5), (5, 400, 128, 64, 2),
+                                             (4, 9000, 1024, 4096, 0), (2, 3000, 1024, 700, 0), (3, 50, 1024, 120, 0)])
 def test_multi_replicas_on_one_gpu_take_local_steps(sl, orc, W, n, F, B, variant):
     # sl_train_steps_multi: the SMs are cut into W partitions, worker k trains its own model on its own
     # shard; every worker must equal (a) the oracle on its shard and (b), bit for bit, the same worker
@@ -600,8 +601,12 @@ def test_multi_replicas_on_one_gpu_take_local_steps(sl, orc, W, n, F, B, variant
             r.load_shard(X, y)
         reps[0].set_option("variant", variant)
         lg = np.concatenate([sl.Replica.train_steps_multi(reps, 4), sl.Replica.train_steps_multi(reps, steps - 4)], axis=1)
-        grid = reps[0].info("grid") // W
-        assert reps[0].info("path") == 1 and grid >= 1
+        # W <= 4 and F <= 1024 run interleaved on every SM (path 5: the full grid per replica), otherwise the
+        # SMs are cut into W partitions (path 1)
+        path = reps[0].info("path")
+        assert path in (1, 5)
+        grid = reps[0].info("grid") // (W if path == 1 else 1)
+        assert grid >= 1
         for k, r in enumerate(reps):
             ref = np.zeros(F)
             lo = orc.lr_steps(*shards[k], B, 0, steps, ref, eta)
@@ -612,7 +617,10 @@ def test_multi_replicas_on_one_gpu_take_local_steps(sl, orc, W, n, F, B, variant
                 solo.set_option("variant", variant)
                 solo.set_option("grid", grid)
                 ls = solo.train_steps(steps)
-                assert np.array_equal(solo.model(), r.model()) and np.array_equal(ls, lg[k]), k
+                if path == 1 or F == 1024:      # same arithmetic as the solo kernel: bit for bit
+                    assert np.array_equal(solo.model(), r.model()) and np.array_equal(ls, lg[k]), k
+                else:                           # narrower rows: the solo kernel groups rows differently
+                    assert w_err(solo.model(), r.model()) <= W_TOL
     finally:
         for r in reps:
             r.close()
