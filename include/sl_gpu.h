@@ -191,12 +191,13 @@ int sl_train_steps_sync(sl_handle* h, int n_steps, double* loss_out);
 int sl_train_steps_group(sl_handle* const* handles, int W, int n_steps, double* loss_out);
 /* W worker replicas that share one GPU each take n_steps LOCAL steps — the reference's own structure
  * (every worker process runs its own training thread, src/worker.cc:221-231,246, and only gossip
- * couples them): independent models, nothing summed across workers.  One persistent kernel: the SMs
- * are cut into W equal partitions, partition k trains handles[k]'s model on handles[k]'s shard with
- * its own accumulators and counter, so the W workers advance side by side instead of queueing W
- * whole-GPU kernels.  Same requirements as sl_train_steps_group, and F <= 2048 (register-row
- * kernel).  Worker k ends bit-identical to sl_train_steps on its own with "grid" = SMs / W.
- * loss_out (nullable): W * n_steps doubles, worker-major.  No reference counterpart. */
+ * couples them): independent models, nothing summed across workers.  One persistent kernel.  For
+ * W <= 4 and F <= 1024 the replicas are interleaved on every SM (the exchange of one model's step
+ * hides behind the compute of the others; every worker ends bit-identical to sl_train_steps on its
+ * own); otherwise the SMs are cut into W equal partitions (W <= 8, F <= 2048; every worker ends
+ * bit-identical to sl_train_steps on its own with "grid" = SMs / W).  Same requirements as
+ * sl_train_steps_group.  loss_out (nullable): W * n_steps doubles, worker-major.  No reference
+ * counterpart. */
 int sl_train_steps_multi(sl_handle* const* handles, int W, int n_steps, double* loss_out);
 
 /* ---- allocation-free step ------------------------------------------------------------
