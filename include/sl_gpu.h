@@ -194,7 +194,8 @@ int sl_train_steps_group(sl_handle* const* handles, int W, int n_steps, double* 
  * couples them): independent models, nothing summed across workers.  One persistent kernel.  For
  * W <= 4 and F <= 1024 the replicas are interleaved on every SM (the exchange of one model's step
  * hides behind the compute of the others; every worker ends bit-identical to sl_train_steps on its
- * own); otherwise the SMs are cut into W equal partitions (W <= 8, F <= 2048; every worker ends
+ * own at F = 1024, within fp32 rounding of it for narrower rows, which the solo kernel groups
+ * differently); otherwise the SMs are cut into W equal partitions (W <= 8, F <= 2048; every worker ends
  * bit-identical to sl_train_steps on its own with "grid" = SMs / W).  Same requirements as
  * sl_train_steps_group.  loss_out (nullable): W * n_steps doubles, worker-major.  No reference
  * counterpart. */
