@@ -122,7 +122,10 @@ __global__ void __launch_bounds__((NCW + 1 + (NM + LPW - 1) / LPW) * 32, 1) lr_i
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
                 asm volatile("fence.proxy.async;" ::: "memory");
-                red_release_add_u32(counter, 1u);
+                if (a.relaxed_signal)  // experiment, see DESIGN.md §4
+                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(counter), "r"(1u) : "memory");
+                else
+                    red_release_add_u32(counter, 1u);
                 const unsigned want = (unsigned)G * (unsigned)(s + 1);
                 uint32_t spins = 0;
                 while ((int)(ld_relaxed_u32(counter) - want) < 0) {
@@ -198,28 +201,34 @@ __global__ void __launch_bounds__((NCW + 1 + (NM + LPW - 1) / LPW) * 32, 1) lr_i
                 else y_next = (s + 1 < a.n_steps) ? load_y(mb_next, 0, 0) : 0.f;
                 float4 x[R];
                 {
+                    // wait for all slots of the pass, issue every load, and only then hand the slots back:
+                    // one exposed latency per pass instead of one per slot
                     uint32_t sl = base_slot + (uint32_t)(sb * SPB);
                     uint32_t k = sl / (uint32_t)ns;
                     uint32_t slot = sl - k * (uint32_t)ns;
                     uint32_t par = (base_phase ^ k) & 1u;
+                    uint32_t slot_of[SPB];
 #pragma unroll
                     for (int q = 0; q < SPB; ++q) {
-                        if (q * RS < rc) {  // warp-uniform
-                            mbar_wait(smem_u32(&full[slot]), par, a.err);
-                            const uint32_t sbase = smem_u32(ring + (size_t)slot * slot_bytes);
+                        slot_of[q] = slot;
+                        if (q * RS < rc) mbar_wait(smem_u32(&full[slot]), par, a.err);  // warp-uniform
+                        if (++slot == (uint32_t)ns) { slot = 0; par ^= 1u; }
+                    }
 #pragma unroll
-                            for (int rr = 0; rr < RS; ++rr) {
-                                const int r = q * RS + rr;
-                                x[r] = (gv && r < rc) ? lds_v4(sbase + (uint32_t)rr * (uint32_t)row_bytes + (uint32_t)tid * 16u)
-                                                      : make_float4(0.f, 0.f, 0.f, 0.f);
-                            }
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(smem_u32(&empty[slot]));  // rows are in registers
-                            if (++slot == (uint32_t)ns) { slot = 0; par ^= 1u; }
-                        } else {
+                    for (int q = 0; q < SPB; ++q) {
+                        const uint32_t sbase = smem_u32(ring + (size_t)slot_of[q] * slot_bytes);
 #pragma unroll
-                            for (int rr = 0; rr < RS; ++rr) x[q * RS + rr] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int rr = 0; rr < RS; ++rr) {
+                            const int r = q * RS + rr;
+                            x[r] = (gv && r < rc) ? lds_v4(sbase + (uint32_t)rr * (uint32_t)row_bytes + (uint32_t)tid * 16u)
+                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
                         }
+                    }
+                    __syncwarp();
+                    if (lane == 0) {
+#pragma unroll
+                        for (int q = 0; q < SPB; ++q)
+                            if (q * RS < rc) mbar_arrive(smem_u32(&empty[slot_of[q]]));  // rows are in registers
                     }
                 }
                 if (sb == 0 && s > 0) apply_total();

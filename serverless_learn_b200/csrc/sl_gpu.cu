@@ -652,6 +652,7 @@ int run_interleaved(sl_handle* h, int n_steps, bool want_loss) {
         a.eta_over_b = h->eta / (double)h->B;
         a.err = h->d_err;
         a.tma_chunk = 1 << 20;
+        a.relaxed_signal = h->opt_relaxed_signal != 0 ? 1 : 0;
         for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; a.pmodel[k] = h->pmodel[k]; }
         CK(h, cudaMemsetAsync(h->acc, 0, need, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 256, h->stream));
