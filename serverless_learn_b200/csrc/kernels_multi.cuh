@@ -33,9 +33,14 @@ __global__ void __launch_bounds__((NCW + 1 + (NM + LPW - 1) / LPW) * 32, 1) lr_i
     uint64_t* wfull = gfull + NM;                                      // [NM] total of model m landed
     float* red = reinterpret_cast<float*>(smem + a.off_red);          // [2][NCW][R]
     float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);          // [2][zy_rows]
-    long long* gout = reinterpret_cast<long long*>(smem + a.off_gout);  // [NM][Fp] staged gradients
-    long long* gin = reinterpret_cast<long long*>(smem + a.off_gin);    // [NM][Fp] landed totals
-    double* msm = reinterpret_cast<double*>(smem + a.off_msm);        // [NM][F] fp64 masters
+    // one s64 vector per model: first the CTA's staged gradient (source of the bulk reduction), later the
+    // landed total of the same step (the reduction has read the buffer long before the total arrives, and
+    // the next gradient is staged only after the total has been applied)
+    long long* gout = reinterpret_cast<long long*>(smem + a.off_gout);  // [NM][Fp]
+    long long* gin = gout;
+    // fp64 masters: this CTA's private copy in global memory (stays in L2), [NM][F]; only the thread that
+    // owns a column chunk ever touches its four doubles.  Shared memory goes to the row ring instead.
+    double* msm = a.wmaster + (size_t)blockIdx.x * NM * (size_t)a.F;
 
     const int F = a.F, Fp = a.Fp, ns = a.ns, row_bytes = a.row_bytes;
     const uint32_t slot_bytes = (uint32_t)RS * (uint32_t)row_bytes;
@@ -156,7 +161,8 @@ __global__ void __launch_bounds__((NCW + 1 + (NM + LPW - 1) / LPW) * 32, 1) lr_i
         if (gv) {
             const double* src = a.pmodel[m] + tid * 4;
             double* mm = msm + (size_t)m * F + tid * 4;
-            mm[0] = src[0]; mm[1] = src[1]; mm[2] = src[2]; mm[3] = src[3];
+            __stcg(reinterpret_cast<double2*>(mm), make_double2(src[0], src[1]));
+            __stcg(reinterpret_cast<double2*>(mm) + 1, make_double2(src[2], src[3]));
             w[m] = make_float4((float)src[0], (float)src[1], (float)src[2], (float)src[3]);
         }
     }
@@ -176,16 +182,22 @@ __global__ void __launch_bounds__((NCW + 1 + (NM + LPW - 1) / LPW) * 32, 1) lr_i
         for (int m = 0; m < NM; ++m) {
             // the gradient total of (s-1, m) has had NM-1 virtual steps to arrive
             auto apply_total = [&]() {
+                double2 m01 = make_double2(0.0, 0.0), m23 = m01;
+                double* mm = msm + (size_t)m * F + tid * 4;
+                if (gv) {  // the master's L2 round trip overlaps the wait for the total
+                    m01 = __ldcg(reinterpret_cast<const double2*>(mm));
+                    m23 = __ldcg(reinterpret_cast<const double2*>(mm) + 1);
+                }
                 mbar_wait(smem_u32(&wfull[m]), (uint32_t)(s - 1) & 1u, a.err);
                 if (gv) {
                     const longlong2* p = reinterpret_cast<const longlong2*>(gin + (size_t)m * Fp + tid * 4);
                     const longlong2 u = p[0], v = p[1];
-                    double* mm = msm + (size_t)m * F + tid * 4;
-                    const double v0 = mm[0] - a.eta_over_b * ((double)u.x * kFixInv);
-                    const double v1 = mm[1] - a.eta_over_b * ((double)u.y * kFixInv);
-                    const double v2 = mm[2] - a.eta_over_b * ((double)v.x * kFixInv);
-                    const double v3 = mm[3] - a.eta_over_b * ((double)v.y * kFixInv);
-                    mm[0] = v0; mm[1] = v1; mm[2] = v2; mm[3] = v3;
+                    const double v0 = m01.x - a.eta_over_b * ((double)u.x * kFixInv);
+                    const double v1 = m01.y - a.eta_over_b * ((double)u.y * kFixInv);
+                    const double v2 = m23.x - a.eta_over_b * ((double)v.x * kFixInv);
+                    const double v3 = m23.y - a.eta_over_b * ((double)v.y * kFixInv);
+                    __stcg(reinterpret_cast<double2*>(mm), make_double2(v0, v1));
+                    __stcg(reinterpret_cast<double2*>(mm) + 1, make_double2(v2, v3));
                     w[m] = make_float4((float)v0, (float)v1, (float)v2, (float)v3);
                 }
             };
@@ -293,29 +305,24 @@ __global__ void __launch_bounds__((NCW + 1 + (NM + LPW - 1) / LPW) * 32, 1) lr_i
         mb = mb_next;
     }
 
-    // the last totals, then the masters back to global (all CTAs hold identical copies: CTA 0 writes)
+    // the last totals, then the masters to the replicas' models (all CTAs hold identical copies: CTA 0 writes)
     if (a.n_steps > 0) {
         const int s = a.n_steps;
 #pragma unroll
         for (int m = 0; m < NM; ++m) {
             mbar_wait(smem_u32(&wfull[m]), (uint32_t)(s - 1) & 1u, a.err);
-            if (gv) {
+            if (gv && c == 0) {
                 const longlong2* p = reinterpret_cast<const longlong2*>(gin + (size_t)m * Fp + tid * 4);
                 const longlong2 u = p[0], v = p[1];
-                double* mm = msm + (size_t)m * F + tid * 4;
-                mm[0] -= a.eta_over_b * ((double)u.x * kFixInv);
-                mm[1] -= a.eta_over_b * ((double)u.y * kFixInv);
-                mm[2] -= a.eta_over_b * ((double)v.x * kFixInv);
-                mm[3] -= a.eta_over_b * ((double)v.y * kFixInv);
+                const double* mm = msm + (size_t)m * F + tid * 4;
+                const double2 m01 = __ldcg(reinterpret_cast<const double2*>(mm));
+                const double2 m23 = __ldcg(reinterpret_cast<const double2*>(mm) + 1);
+                double* dst = a.pmodel[m] + tid * 4;
+                dst[0] = m01.x - a.eta_over_b * ((double)u.x * kFixInv);
+                dst[1] = m01.y - a.eta_over_b * ((double)u.y * kFixInv);
+                dst[2] = m23.x - a.eta_over_b * ((double)v.x * kFixInv);
+                dst[3] = m23.y - a.eta_over_b * ((double)v.y * kFixInv);
             }
-        }
-    }
-    if (c == 0 && gv) {
-#pragma unroll
-        for (int m = 0; m < NM; ++m) {
-            const double* mm = msm + (size_t)m * F + tid * 4;
-            double* dst = a.pmodel[m] + tid * 4;
-            dst[0] = mm[0]; dst[1] = mm[1]; dst[2] = mm[2]; dst[3] = mm[3];
         }
     }
 }

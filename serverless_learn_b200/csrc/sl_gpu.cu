@@ -112,6 +112,9 @@ const Variant kVariants[] = {
     SL_WIDE(4, 16, 4, 2),             // 24: F <= 2048,  four groups, two rows per pass
     SL_WIDE(2, 16, 2, 2),             // 25: F <= 2048,  two groups, two rows per pass
     SL_WIDE(10, 14, 1, 2),            // 26: F <= 17920, one group, two rows per pass
+    SL_VARIANT(1, 16, 8, 8, 1, 0),    // 27: F <= 1024, 8-row ring slots
+    SL_VARIANT(1, 16, 16, 8, 1, 0),   // 28: F <= 1024, one 16-row ring slot per pass: fewer barrier operations per
+                                      //     row; measured best once a CTA has >= ~40 rows per step
 };
 // auto-selection: the first of these that is wide enough for F
 const int kAutoOrder[] = {1, 5, 22, 14, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
@@ -315,6 +318,16 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
             if (granules <= variant_granules(kVariants[i])) { vi = i; break; }
         }
         if (vi < 0) { *why = "F too wide for the persistent kernel"; return false; }
+        // many rows per CTA and step: every ring slot costs each warp a barrier wait and an arrival, so
+        // one slot per pass wins (F=1024, B=16384: 14.3 vs 16.5 us/step); at config 3's 28 rows the
+        // finer slots refill earlier and win (7.3 vs 7.75)
+        {
+            int g = h->num_sms;
+            if (h->opt_grid > 0) g = (int)std::min<long long>(h->opt_grid, h->num_sms);
+            if (h->npart > 1) g = std::max(1, g / h->npart);
+            const long long beff = (long long)h->B * (h->vw > 1 ? h->vw : 1);
+            if (vi == 0 && (beff + g - 1) / g >= 40) vi = 27;  // variant 28
+        }
     }
     const Variant& v = kVariants[vi];
     int grid = h->num_sms;
@@ -583,7 +596,7 @@ int launch_simple_step(sl_handle* h, double* d_loss_slot, bool sync) {
 }
 
 // K1m: NM <= 4 independent replicas interleaved on every SM (kernels_multi.cuh).  F <= 1024.
-constexpr int kIlvR = 16, kIlvRS = 4, kIlvNCW = 8;
+constexpr int kIlvR = 16, kIlvRS = 16, kIlvNCW = 8;
 bool interleaved_ok(const sl_handle* h) {
     return h->npart >= 2 && h->npart <= 4 && h->F % 4 == 0 && h->F <= 4 * 32 * kIlvNCW && h->coop &&
            h->opt_multi_mode == 0 && h->opt_variant == 0;
@@ -608,7 +621,7 @@ int run_interleaved(sl_handle* h, int n_steps, bool want_loss) {
     const size_t red_b = sizeof(float) * 2 * kIlvNCW * kIlvR;
     const size_t zy_b = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
     const size_t vec_b = 8 * (size_t)F * NM;  // gout, gin, masters: one of each per model
-    const size_t fixed = red_b + zy_b + 3 * vec_b + 1024;
+    const size_t fixed = red_b + zy_b + vec_b + 1024;  // one s64 vector per model; the masters live in global scratch
     const size_t slot_b = (size_t)kIlvRS * a.row_bytes;
     if (h->smem_optin < fixed + (slot_b + 16) * (kIlvR / kIlvRS))
         return fail(h, SL_EINVAL, "the interleaved kernel does not fit in shared memory at F = %d", F);
@@ -620,9 +633,17 @@ int run_interleaved(sl_handle* h, int n_steps, bool want_loss) {
     off = align_up(off, 16); a.off_red = (int)off;   off += red_b;
     off = align_up(off, 16); a.off_zy = (int)off;    off += zy_b;
     off = align_up(off, 128); a.off_gout = (int)off; off += vec_b;
-    off = align_up(off, 128); a.off_gin = (int)off;  off += vec_b;
-    off = align_up(off, 16); a.off_msm = (int)off;   off += vec_b;
     const size_t smem = off;
+    {   // per-CTA fp64 masters in global memory (L2)
+        const size_t wb = sizeof(double) * (size_t)grid * NM * F;
+        if (h->wmaster_bytes < wb) {
+            if (h->wmaster) cudaFree(h->wmaster);
+            h->wmaster = nullptr;
+            h->wmaster_bytes = 0;
+            CK(h, cudaMalloc(&h->wmaster, wb));
+            h->wmaster_bytes = wb;
+        }
+    }
     const size_t need = 8 * (size_t)3 * F * NM;
     if (h->acc_bytes < need) {
         if (h->acc) cudaFree(h->acc);
@@ -647,6 +668,7 @@ int run_interleaved(sl_handle* h, int n_steps, bool want_loss) {
         a.n_steps = n;
         a.acc = h->acc;
         a.counter = h->counter;
+        a.wmaster = h->wmaster;
         a.loss_fix = want_loss ? h->loss_fix + done : nullptr;
         a.loss_stride = n_steps;
         a.eta_over_b = h->eta / (double)h->B;
