@@ -115,9 +115,10 @@ const Variant kVariants[] = {
     SL_VARIANT(1, 16, 8, 8, 1, 0),    // 27: F <= 1024, 8-row ring slots
     SL_VARIANT(1, 16, 16, 8, 1, 0),   // 28: F <= 1024, one 16-row ring slot per pass: fewer barrier operations per
                                       //     row; measured best once a CTA has >= ~40 rows per step
+    SL_VARIANT(2, 8, 8, 8, 1, 0),     // 29: F <= 2048, one 8-row ring slot per pass
 };
 // auto-selection: the first of these that is wide enough for F
-const int kAutoOrder[] = {1, 5, 22, 14, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
+const int kAutoOrder[] = {1, 29, 22, 14, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 }  // namespace

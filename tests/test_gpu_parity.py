@@ -178,7 +178,7 @@ def test_lr_golden_cases(sl, orc, name, path):
     assert w_err(wg, GOLD[f"{name}_w"]) <= W_TOL
 
 
-@pytest.mark.parametrize("variant", list(range(1, 29)))
+@pytest.mark.parametrize("variant", list(range(1, 30)))
 @pytest.mark.parametrize("shape", [(300, 64, 48), (2000, 1024, 256), (700, 260, 100)])
 def test_lr_all_variants(sl, orc, variant, shape):
     n, F, B = shape
@@ -191,7 +191,7 @@ def test_lr_all_variants(sl, orc, variant, shape):
 @pytest.mark.parametrize("variant,F", [(2, 2048), (4, 2048), (5, 2048), (6, 2048), (6, 4096), (7, 2048), (7, 8192),
                                        (8, 16384), (9, 8192), (11, 16384), (12, 8192), (13, 4096), (14, 8192),
                                        (15, 4096), (16, 4096), (17, 2048), (18, 3072), (19, 1024), (20, 8192), (21, 8192),
-                                       (22, 4096), (23, 5376), (24, 2048), (25, 2048), (26, 16384), (27, 1024), (28, 1024)])
+                                       (22, 4096), (23, 5376), (24, 2048), (25, 2048), (26, 16384), (27, 1024), (28, 1024), (29, 2048)])
 def test_lr_variants_at_full_width(sl, orc, variant, F):
     ew, el, info, _, _ = _run_case(sl, orc, 400, F, 160, 6, 0.2, 1, variant=variant)
     assert info[:2] == (1, variant)
