@@ -87,7 +87,9 @@ int sl_debug_read(sl_handle* h, unsigned long long* out, size_t n_words);
  * length, and with SL_SHARD_HAS_SUMS the payload's byte sum and weighted sum (the
  * sl_shard_checksum quantities, over the bytes after the header) must match — and the payload
  * after the header is what gets trained on.  A mismatch fails sl_shard_end (SL_EINVAL) and keeps
- * the previously sealed shard.  Streams without the magic are taken verbatim as before. */
+ * the previously sealed shard.  Streams without the magic are taken verbatim as before.
+ * A stream that does not hold one complete row seals nothing: sl_shard_end returns SL_OK with
+ * *n_rows = 0 and the previously sealed shard (if any) stays the one that is trained on. */
 #define SL_SHARD_MAGIC "SLSHARD\1"
 #define SL_SHARD_HAS_SUMS 1u
 typedef struct sl_shard_header {   /* little-endian, 64 bytes */
@@ -170,8 +172,10 @@ int sl_gossip_p2p(sl_handle* initiator, sl_handle* callee);
  * in one persistent kernel per GPU: the kernels exchange 32-element slices of the exact integer
  * gradient sum through peer-mapped memory over NVLink, no host-launched collective per step.
  * Every rank must call sl_train_steps_sync with the same n_steps at about the same time (the
- * kernels wait for one another).  With NCCL also initialised the returned losses are the mean
- * over ranks, otherwise this rank's own.  Option "sync_path" = 1 forces the NCCL path. */
+ * kernels wait for one another).  loss_out: with NCCL also initialised (sl_comm_init_rank) the
+ * returned losses are the mean over ranks; with sl_peer_attach alone they are THIS rank's own
+ * minibatch losses (the models are identical on all ranks either way).  Option "sync_path" = 1
+ * forces the NCCL path; a shape the fused kernels cannot run needs NCCL too (SL_ESTATE otherwise). */
 int sl_peer_export(sl_handle* h, void* handle64);
 int sl_peer_attach(sl_handle* h, int nranks, int rank, const void* handles);
 int sl_comm_unique_id(void* id128);
@@ -214,6 +218,8 @@ int sl_train_steps_multi(sl_handle* const* handles, int W, int n_steps, double* 
  * until the process exits).
  *   - d_X [n_rows*F] fp32, d_y [n_rows] fp32, d_model [F] fp64 (updated in place) and
  *     d_loss (nullable, 1 fp64) are DEVICE pointers on `device`, owned by the caller.
+ *     When F is a multiple of 4 the rows are read 16 bytes at a time: d_X must then be
+ *     16-byte aligned (SL_EINVAL otherwise — a view into the middle of a larger buffer may not be).
  *   - limits: B <= 8192, F <= 4096; larger shapes return SL_EINVAL (see sl_last_error(NULL)).
  *   - asynchronous: the three kernels are enqueued on `stream` (a cudaStream_t, NULL = the
  *     default stream); results are ready when the stream reaches that point.

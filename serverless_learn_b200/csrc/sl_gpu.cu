@@ -524,7 +524,6 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
             a.xflag0 = h->xflag_base;
             a.n_own = (h->F + plan.args.xslice - 1) / plan.args.xslice;
             a.eta_over_b = h->eta / ((double)h->B * (double)h->peer_n);
-            h->xflag_base += (unsigned)n;
         }
         a.err = h->d_err;
         a.dbg = nullptr;
@@ -544,6 +543,7 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         void* params[] = {&a};
         CK(h, cudaLaunchCooperativeKernel(v.fn, dim3(plan.grid), dim3((v.ncw + 2 - v.kind) * 32), params,
                                           plan.smem, h->stream));
+        if (fused_sync) h->xflag_base += (unsigned)n;  // only a launch that went out consumes packet flags
         h->launches++;
         h->k1_launches++;
         h->step += n;
@@ -581,6 +581,7 @@ int launch_simple_step(sl_handle* h, double* d_loss_slot, bool sync) {
                                                      sync ? 1 : 0);
     h->launches += 3;
     if (sync) {
+        if (!h->comm || !g_nccl.AllReduce) return fail(h, SL_ESTATE, "no NCCL communicator (sl_comm_init_rank)");
         int nrc = g_nccl.AllReduce(h->gsum, h->gsum, (size_t)h->F + 1, kNcclFloat64, kNcclSum,
                                    h->comm, h->stream);
         if (nrc != 0)
@@ -740,6 +741,9 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     }
     if (!sync && h->opt_path == 1 && !persist)
         return fail(h, SL_EINVAL, "persistent path requested but unavailable: %s", why.c_str());
+    if (sync && !fused && (!h->comm || !g_nccl.AllReduce))
+        return fail(h, SL_ESTATE, "the fused peer path cannot run this shape (%s) and no NCCL communicator "
+                    "is initialised (sl_comm_init_rank)", why.empty() ? "not eligible" : why.c_str());
     CK(h, cudaEventRecord(h->ev0, h->stream));
     if (persist || fused) {
         rc = run_persist(h, plan, n_steps, loss_out != nullptr, fused);
@@ -1007,7 +1011,12 @@ int sl_shard_end(sl_handle* h, long long* n_rows) {
             h->in_len = 0;
             if (hd.version != 1) return fail(h, SL_EINVAL, "shard header version %u not understood", hd.version);
             if ((int)hd.F != h->F) return fail(h, SL_EINVAL, "shard was written for F = %u, this replica has F = %d", hd.F, h->F);
-            const unsigned long long want = sizeof(hd) + hd.n_rows * 4ull * ((unsigned long long)h->F + 1);
+            // bound n_rows by the stream length before multiplying: a crafted count must not wrap
+            const unsigned long long row_b = 4ull * ((unsigned long long)h->F + 1);
+            if (hd.n_rows > (in_len - sizeof(hd)) / row_b)
+                return fail(h, SL_EINVAL, "shard header promises %llu rows, the stream has room for %llu",
+                            hd.n_rows, (unsigned long long)((in_len - sizeof(hd)) / row_b));
+            const unsigned long long want = sizeof(hd) + hd.n_rows * row_b;
             if (want != in_len)
                 return fail(h, SL_EINVAL, "shard header promises %llu bytes, the stream had %zu", want, in_len);
             if (hd.flags & SL_SHARD_HAS_SUMS) {
@@ -1027,6 +1036,14 @@ int sl_shard_end(sl_handle* h, long long* n_rows) {
             rows = (long long)hd.n_rows;
             h->in_len = in_len;
         }
+    }
+    if (rows <= 0) {
+        // a stream without one complete row seals nothing: whatever shard was trainable before stays
+        // (the reference acks such a stream like any other, src/worker.cc:57-60, so this is no error)
+        h->in_len = 0;
+        h->shard_open = false;
+        if (n_rows) *n_rows = 0;
+        return SL_OK;
     }
     std::swap(h->shard, h->in_buf);
     std::swap(h->shard_cap, h->in_cap);
@@ -1480,6 +1497,9 @@ extern "C" int sl_lr_step_noalloc(int device, const float* d_X, const float* d_y
                     B, F, SL_NOALLOC_MAX_B, SL_NOALLOC_MAX_F);
     if (device < 0 || device >= kNaMaxDevices)
         return fail(nullptr, SL_EINVAL, "sl_lr_step_noalloc: device %d out of range", device);
+    if (F % 4 == 0 && ((uintptr_t)d_X & 15) != 0)
+        return fail(nullptr, SL_EINVAL, "sl_lr_step_noalloc: d_X must be 16-byte aligned when F is a multiple of 4 "
+                    "(rows are read as float4)");
     DeviceGuard dg(device);
     unsigned char* base = nullptr;
     int sms = 0;

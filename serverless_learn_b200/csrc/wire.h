@@ -38,9 +38,11 @@ inline int update_decode(const void* buf_, long len, double* out, int cap) {
                 l |= (uint64_t)(b & 0x7F) << shift;
                 if (!(b & 0x80)) break;
             }
-            if (l % 8 != 0 || pos + (long)l > len) return -1;
+            // lengths are compared unsigned and bounded by what is left of the buffer and of
+            // `out` BEFORE any narrowing: a varint of 2^63 would otherwise turn negative
+            if (l % 8 != 0 || l > (uint64_t)(len - pos)) return -1;
+            if (l / 8 > (uint64_t)(cap - n)) return -1;
             const int k = (int)(l / 8);
-            if (n + k > cap) return -1;
             memcpy(out + n, buf + pos, l);
             n += k;
             pos += (long)l;

@@ -632,3 +632,43 @@ def test_multi_rejects_wide_rows(sl, orc):
         a.load_shard(X, y); b.load_shard(X, y)
         with pytest.raises(sl.SlError):
             sl.Replica.train_steps_multi([a, b], 1)
+
+
+def test_sync_without_nccl_on_a_shape_the_fused_path_cannot_run_fails_cleanly(sl, orc):
+    """Peers attached, NCCL never initialised, F % 4 != 0 (the persistent kernels cannot run it): the
+    call must come back with SL_ESTATE instead of reaching for a communicator that does not exist."""
+    n, F, B = 64, 7, 16
+    X, y = orc.synth(0, n, F)
+    with sl.Replica(F, B) as r:
+        r.load_shard(X, y)
+        r.peer_attach(1, 0, r.peer_export())
+        with pytest.raises(sl.SlError) as ei:
+            r.train_steps_sync(2)
+        assert ei.value.code == -3
+        assert r.train_steps(2) is not None      # the handle stays usable
+
+
+def test_stream_without_a_complete_row_keeps_the_sealed_shard(sl, orc):
+    n, F, B = 96, 64, 32
+    X, y = orc.synth(0, n, F)
+    with sl.Replica(F, B, eta=0.2) as r:
+        r.load_shard(X, y)
+        r.train_steps(2)
+        r.shard_begin(0)
+        r.shard_append(np.zeros(100, dtype=np.uint8))     # less than one 260-byte row
+        assert r.shard_end() == 0
+        assert r.info("n_rows") == n and r.info("step") == 2
+        ref = np.zeros(F)
+        orc.lr_steps(X, y, B, 0, 4, ref, 0.2)
+        r.train_steps(2)
+        assert w_err(r.model(), ref) <= W_TOL
+        # a header whose row count would wrap the length check in 64 bits is refused
+        hd = bytearray(_described(X[:1], y[:1])[:64])
+        assert ((((1 << 62) + 1) * 4 * (F + 1)) % (1 << 64)) == 4 * (F + 1)    # F + 1 = 65 is odd
+        hd[16:24] = ((1 << 62) + 1).to_bytes(8, "little")
+        hd[32:36] = (0).to_bytes(4, "little")          # no sums to check
+        r.shard_begin(0)
+        r.shard_append(bytes(hd) + bytes(4 * (F + 1)))
+        with pytest.raises(sl.SlError):
+            r.shard_end()
+        assert r.info("n_rows") == n

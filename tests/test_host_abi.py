@@ -86,6 +86,13 @@ def test_wire_codec_matches_oracle(libs, orc):
     assert buf.raw[:w].hex() == "0a18000000000000f03f00000000000004c00000000000000000"   # B.5
     assert L.slr_update_encode(d.ctypes.data_as(dp), 3, buf, 10) == -1
     assert L.slr_update_decode(b"\x0a\x07" + b"\0" * 7, 9, d.ctypes.data_as(dp), 3) == -1
+    # malformed lengths from the wire: 2^63 (negative once narrowed), 2^32 + 8 (truncates to 1
+    # element), and a length that only exceeds the output capacity — all refused, nothing copied
+    guard = np.full(4, 7.0)
+    for varint in (b"\x80" * 9 + b"\x01", b"\x88\x80\x80\x80\x10", b"\x20"):
+        msg = b"\x0a" + varint + b"\0" * 64
+        assert L.slr_update_decode(msg, len(msg), guard.ctypes.data_as(dp), 3) == -1
+        assert np.array_equal(guard, np.full(4, 7.0))
 
 
 # ---- file server (src/file_server.cc) ----------------------------------------------------

@@ -69,3 +69,42 @@ def test_noalloc_rejects_oversize():
     assert b"8192" in L.sl_last_error(None)
     assert L.sl_lr_step_noalloc(0, p, p, 10, 4100, 8, 0, 0.1, p, None, None) == -1
     assert L.sl_lr_step_noalloc(0, None, p, 10, 4, 8, 0, 0.1, p, None, None) == -1
+
+
+def test_noalloc_rejects_misaligned_rows():
+    """With F a multiple of 4 the rows are read 16 bytes at a time: a view 4 bytes into a buffer is
+    refused up front instead of faulting on the device; F not a multiple of 4 takes any alignment."""
+    import torch
+
+    from serverless_learn_b200 import _lib
+
+    L = _lib.load()
+    buf = torch.zeros(1024, dtype=torch.float32, device="cuda:0")
+    w = torch.zeros(8, dtype=torch.float64, device="cuda:0")
+    assert L.sl_lr_step_noalloc(0, buf.data_ptr() + 4, buf.data_ptr(), 10, 8, 4, 0, 0.1, w.data_ptr(), None, None) == -1
+    assert b"aligned" in L.sl_last_error(None)
+    assert L.sl_lr_step_noalloc(0, buf.data_ptr() + 4, buf.data_ptr(), 10, 7, 4, 0, 0.1, w.data_ptr(), None, None) == 0
+    torch.cuda.synchronize()
+
+
+def test_noalloc_at_its_limits(orc):
+    """B = 8192 and F = 4096, the largest shape the built-in scratch takes, against the oracle."""
+    import torch
+
+    from serverless_learn_b200 import _lib
+
+    L = _lib.load()
+    n, F, B, eta = 8192, 4096, 8192, 0.1
+    X, y = orc.synth(0, n, F)
+    dev = torch.device("cuda", 0)
+    dX, dy = torch.from_numpy(X).to(dev), torch.from_numpy(y).to(dev)
+    dw = torch.zeros(F, dtype=torch.float64, device=dev)
+    dl = torch.zeros(2, dtype=torch.float64, device=dev)
+    for t in range(2):
+        assert L.sl_lr_step_noalloc(0, dX.data_ptr(), dy.data_ptr(), n, F, B, t, eta, dw.data_ptr(),
+                                    dl.data_ptr() + 8 * t, None) == 0, L.sl_last_error(None)
+    torch.cuda.synchronize()
+    w = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, 2, w, eta)
+    assert np.max(np.abs(dw.cpu().numpy() - w)) / np.max(np.abs(w)) <= W_TOL
+    assert np.max(np.abs(dl.cpu().numpy() - lo) / lo) <= L_TOL
