@@ -21,7 +21,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 TARGETS = {
     "libsl_gpu.so": dict(
-        srcs=["sl_gpu.cu"], deps=["kernels.cuh", "kernels_wide.cuh", "kernels_multi.cuh", "../../include/sl_gpu.h"],
+        srcs=["sl_gpu.cu"], deps=["kernels.cuh", "kernels_wide.cuh", "kernels_multi.cuh", "kernels_cluster.cuh", "../../include/sl_gpu.h"],
         cmd=lambda out, srcs: [NVCC, *ARCH, "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
                                "-shared", "-cudart", "static", "-o", out, *srcs, "-ldl"]),
     "libsl_roles.so": dict(

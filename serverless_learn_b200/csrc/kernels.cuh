@@ -309,7 +309,8 @@ struct RowRef {
     const float* y;
     long long room;
 };
-__device__ __forceinline__ RowRef locate_row(const LrArgs& a, long long mb, long long p, int part = 0) {
+template <class Args>
+__device__ __forceinline__ RowRef locate_row(const Args& a, long long mb, long long p, int part = 0) {
     const float* X = a.npart > 1 ? a.vX[part] : a.X;
     const float* y = a.npart > 1 ? a.vy[part] : a.y;
     long long r = p, lim = a.n_rows;
@@ -333,7 +334,8 @@ __device__ __forceinline__ RowRef locate_row(const LrArgs& a, long long mb, long
     return ref;
 }
 
-__device__ __forceinline__ void dbg_stamp(const LrArgs& a, int s, int point) {
+template <class Args>
+__device__ __forceinline__ void dbg_stamp(const Args& a, int s, int point) {
     if (a.dbg != nullptr && s >= a.dbg_step && s < a.dbg_step + 4) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

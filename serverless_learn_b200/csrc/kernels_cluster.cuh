@@ -1,0 +1,566 @@
+// kernels_cluster.cuh — K1c: the minibatch step for narrow rows (F <= 1024) as thread-block clusters.
+//
+// lr_persist_kernel's step is one long latency chain (compute -> L2 bulk reduction -> release fence ->
+// arrival counter -> poll -> TMA load of the total: ~5 us of exchange for 2.6 us of HBM streaming at
+// config 3, profiles/r1_timeline.md).  This kernel keeps the row ring and the per-thread arithmetic and
+// replaces the exchange by three fence-free hops:
+//
+//   1. reduce-scatter inside a cluster of CS CTAs through distributed shared memory: every compute
+//      thread sends its fp32 gradient chunk straight from registers to the CTA that owns those columns
+//      (st.async, completion counted in bytes on the owner's mbarrier) — no staging, no barrier;
+//   2. ONE hop through L2 between the clusters: the owner converts every partial to fixed point, adds
+//      the integers and adds the cluster's sum into a global accumulator with a single red.add.u64 whose
+//      low bits count arrivals ((sum << 6) + 1).  Readers poll the accumulator itself until the count
+//      says every cluster has added: data and "flag" are one word, so there is no release fence and no
+//      separate counter.  Accumulators are never cleared: a reader subtracts the value it saw complete
+//      two steps earlier (two buffers, by step parity), arithmetic mod 2^64;
+//   3. the owner applies the total to ITS fp64 master weights (the owner of a column is the only place
+//      they live; all clusters hold identical copies) and sends the new fp32 weights to the CS CTAs of
+//      its cluster (st.async again); compute threads only ever see fp32 weights in shared memory.
+//
+// Integer sums commute: the result does not depend on arrival order, every cluster (and every GPU)
+// computes the same bits.  With peers attached (sl_peer_attach) a fourth hop sums the GPUs' totals the
+// same way over NVLink: add-with-count into every rank's accumulator (one multimem.red through the
+// NVSwitch when a multicast mapping was attached, else one red per peer), poll the own copy.
+//
+// The per-step loss travels the same road one step late, off the critical path, and is written by the
+// kernel itself as a double: no memset before and no conversion kernel after a launch.
+//
+// Takes the slot of simulate_training (src/worker.cc:221-231) like lr_persist_kernel.
+#pragma once
+#include "kernels.cuh"
+
+namespace slk {
+
+constexpr int kClCntBits = 6;                                  // arrivals per word: up to 63 adders
+constexpr unsigned long long kClCntMask = (1ull << kClCntBits) - 1ull;
+constexpr double kClFixInv = 1.0 / 4294967296.0;               // fixed point: 2^-32 units
+constexpr int kErrRange = 5;                                   // a gradient partial left the fixed-point range
+
+struct ClArgs {
+    const float* X;        // [n_rows, F] row-major, resident shard
+    const float* y;        // [n_rows]
+    long long n_rows;
+    int F;
+    int B;                 // positions per step (nvw * vB in group mode)
+    long long step0;       // global step index of the first step of this launch
+    int n_steps;
+    double* model;         // fp64 master weights [F] (model_state, src/master.cc:58)
+    unsigned long long* gacc;    // [2][F] gradient accumulators: (sum << 6) + arrivals, never cleared
+    unsigned long long* gbase;   // [2][F] their values when the previous launch ended
+    unsigned long long* lacc;    // [2]    loss accumulators, same encoding
+    unsigned long long* lbase;   // [2]
+    double* loss_out;      // device [n_steps]: mean loss of every step, written by the kernel; or nullptr
+    long long xstep0;      // accumulator parity of this launch's first step (continues across launches)
+    // same-box data parallel: one kernel per GPU, totals summed through peer-mapped memory
+    int nranks, rank;      // nranks <= 1: single GPU
+    unsigned long long* peer_gx[8];  // rank p's cross-GPU accumulators [2][F] as mapped here (own = local)
+    unsigned long long* mc_gx;       // multicast alias of the same words on all ranks, or nullptr
+    unsigned long long* gxbase;      // [2][F] own accumulators' values when the previous launch ended
+    double eta_over_b;     // eta / (B * ranks)
+    double inv_b;          // 1 / B
+    float part_limit;      // |partial| above this could overflow the accumulator word
+    int* err;              // 0 = ok; set by the watchdog
+    // geometry, computed on the host
+    int ncl;               // clusters in the grid
+    int fc;                // columns owned by one CTA of a cluster = F / CS
+    int nsg;               // ring slots per row group
+    int row_bytes;         // 4*F
+    int zy_rows;
+    int off_bar, off_recv, off_wsm, off_lrecv, off_red, off_zy;  // smem offsets
+    unsigned long long* dbg;
+    int dbg_step;
+    // several worker replicas on ONE GPU trained as one job (sl_train_steps_group), as in LrArgs
+    int nvw;
+    int vB;
+    int npart;             // always 0 here (locate_row reads it)
+    const float* vX[8];
+    const float* vy[8];
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t cluster_id_x() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// 16 / 4 bytes from registers into another CTA's shared memory; the bytes are counted on that CTA's mbarrier
+__device__ __forceinline__ void st_async_v4(uint32_t raddr, float4 v, uint32_t rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1,%2,%3,%4}, [%5];" ::"r"(raddr),
+                 "r"(__float_as_uint(v.x)), "r"(__float_as_uint(v.y)), "r"(__float_as_uint(v.z)),
+                 "r"(__float_as_uint(v.w)), "r"(rbar)
+                 : "memory");
+}
+__device__ __forceinline__ void st_async_b32(uint32_t raddr, uint32_t v, uint32_t rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(raddr), "r"(v),
+                 "r"(rbar)
+                 : "memory");
+}
+// wait on a barrier whose bytes were written by other CTAs of the cluster
+__device__ __forceinline__ uint32_t mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* err) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait_cluster(bar, parity)) {
+        if (spin_abort(spins, err, kErrTimeoutMbar)) return;
+    }
+}
+__device__ __forceinline__ void red_add_u64_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("multimem.red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// exact: scaling by 2^32 does not round in fp32, the conversion rounds once
+__device__ __forceinline__ long long to_fix32(float v) { return __float2ll_rn(v * 4294967296.0f); }
+
+// Poll an add-with-count word until `want` adders have arrived since `prev`; returns their sum.
+template <bool SYS>
+__device__ __forceinline__ long long poll_total(const unsigned long long* p, unsigned long long& prev, unsigned want,
+                                                int* err, int code, uint32_t limit) {
+    uint32_t spins = 0;
+    unsigned long long v, d;
+    for (;;) {
+        v = SYS ? ld_relaxed_sys_u64(p) : ld_relaxed_u64(p);
+        d = v - prev;
+        if ((d & kClCntMask) == (unsigned long long)want) break;
+        if (spin_abort(spins, err, code, limit)) break;
+    }
+    prev = v;
+    return (long long)(d - (unsigned long long)want) >> kClCntBits;  // exact: the low bits are zero now
+}
+
+// Warps of a CTA: compute, exchange, one producer, padded to whole warpgroups when registers are re-split.
+template <int WPG, int RG, int XW, int CREG>
+constexpr int cl_warps() {
+    return CREG > 0 ? (WPG * RG + XW + 1 + 3) / 4 * 4 : WPG * RG + XW + 1;
+}
+
+// WPG warps cover a row (one float4 column chunk per thread: F <= 128*WPG); RG row groups of WPG warps
+// take R rows each per pass, from their own ring of RS-row slots; CS = CTAs per cluster; XW exchange
+// warps share the (at most 128) columns this CTA owns.  CREG > 0: the compute warpgroups take CREG
+// registers per thread from the exchange / producer warps (setmaxnreg), which keep XREG.
+template <int WPG, int RG, int R, int RS, int CS, int XW, int CREG, int XREG>
+__global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_cluster_kernel(const ClArgs a) {
+    static_assert(R % RS == 0, "a pass is a whole number of ring slots");
+    static_assert(CREG == 0 || (WPG * RG) % 4 == 0, "register re-split needs whole compute warpgroups");
+    constexpr int NCW = WPG * RG;     // compute warps
+    constexpr int XT = XW * 32;       // exchange threads
+    constexpr int XC = (128 + XT - 1) / XT;  // owned columns per exchange thread
+    constexpr int SPB = R / RS;       // ring slots per pass
+    constexpr int NSRC = CS * RG;     // gradient partials an owner receives per step
+    constexpr int CT = WPG * 32;      // threads of a row group
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t crank = cluster_ctarank();
+    const int q = (int)cluster_id_x();
+    const int G = (int)gridDim.x, c = (int)blockIdx.x;
+    const int F = a.F, fc = a.fc, nsg = a.nsg, row_bytes = a.row_bytes, n_steps = a.n_steps;
+    const bool want_loss = a.loss_out != nullptr;
+
+    unsigned char* ring = smem;                                          // [RG][nsg][RS rows]
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.off_bar);      // [RG*nsg]
+    uint64_t* empty = full + RG * nsg;                                   // [RG*nsg]
+    uint64_t* rfull = empty + RG * nsg;                                  // gradient partials of a step landed
+    uint64_t* wfull = rfull + 1;                                         // next step's weights landed
+    uint64_t* lfull = wfull + 1;                                         // [2] loss partials of a step landed
+    float* recv = reinterpret_cast<float*>(smem + a.off_recv);          // [NSRC][fc]
+    float* wsm = reinterpret_cast<float*>(smem + a.off_wsm);            // [2][F]
+    float* lrecv = reinterpret_cast<float*>(smem + a.off_lrecv);        // [2][NSRC]
+    float* red = reinterpret_cast<float*>(smem + a.off_red);            // [2][NCW][R]
+    float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);            // [2][zy_rows]
+
+    const uint32_t slot_bytes = (uint32_t)RS * (uint32_t)row_bytes;
+    const long long lo = ((long long)c * a.B) / G;
+    const long long hi = ((long long)(c + 1) * a.B) / G;
+    const int nrows_c = (int)(hi - lo);             // this CTA's rows of every minibatch
+    const int nst_c = (nrows_c + R - 1) / R;        // ... in passes of R rows
+    const int nsb = (nst_c + RG - 1) / RG;          // passes per row group
+    const long long mb0 = (long long)(((__int128)a.step0 * a.vB) % a.n_rows);
+    auto wrap = [&](long long v) {
+        if (v >= a.n_rows) {
+            v -= a.n_rows;
+            if (v >= a.n_rows) v %= a.n_rows;
+        }
+        return v;
+    };
+    const uint32_t recv_bytes = (uint32_t)NSRC * (uint32_t)fc * 4u;
+
+    if (tid == 0) {
+        for (int s = 0; s < RG * nsg; ++s) {
+            mbar_init(smem_u32(&full[s]), 1);
+            mbar_init(smem_u32(&empty[s]), WPG);
+        }
+        mbar_init(smem_u32(rfull), 1);
+        mbar_init(smem_u32(wfull), 1);
+        mbar_init(smem_u32(&lfull[0]), 1);
+        mbar_init(smem_u32(&lfull[1]), 1);
+        fence_mbar_init();
+        // what the first phases will receive (later phases are armed by their waiters)
+        if (n_steps > 0) mbar_arrive_expect_tx(smem_u32(rfull), recv_bytes);
+        if (n_steps > 1) mbar_arrive_expect_tx(smem_u32(wfull), (uint32_t)F * 4u);
+        if (want_loss && crank == 0) {
+            if (n_steps > 0) mbar_arrive_expect_tx(smem_u32(&lfull[0]), (uint32_t)NSRC * 4u);
+            if (n_steps > 1) mbar_arrive_expect_tx(smem_u32(&lfull[1]), (uint32_t)NSRC * 4u);
+        }
+    }
+    __syncthreads();
+    cluster_sync_all();  // every CTA's barriers exist before anybody stores into a neighbour
+
+    // Register re-split (warpgroup-uniform: the compute warps fill whole warpgroups): every role states its
+    // budget at the top of its own branch.
+    if (warp > NCW + XW) {
+        // padding warp of the last warpgroup: nothing to do
+        if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
+    } else if (warp == NCW + XW) {
+        // ======================================================================= producer
+        if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
+        // Lane l owns ring slot l % nsg of row group l / nsg and fetches that slot's uses over the whole
+        // launch (issuing a slot costs a thread several hundred cycles; one lane would bound the step).
+        const int g = lane / nsg, sl = lane - g * nsg;
+        // slots of one step that belong to group g: passes g, g+RG, ... of SPB slots, the last maybe short
+        int nslg = 0;
+        if (g < RG)
+            for (int j = g; j < nst_c; j += RG) nslg += (min(R, nrows_c - j * R) + RS - 1) / RS;
+        if (g < RG && nslg > 0) {
+            const uint64_t pol = policy_evict_first();
+            const uint32_t eb = smem_u32(&empty[g * nsg + sl]), fb = smem_u32(&full[g * nsg + sl]);
+            const uint32_t dst0 = smem_u32(ring + ((size_t)g * nsg + sl) * slot_bytes);
+            int s = sl / nslg, k = sl - s * nslg;  // step and slot-of-step of this lane's next use
+            uint32_t phase = 0;
+            long long mb = mb0;
+            for (int i = 0; i < s && i < n_steps; ++i) mb = wrap(mb + a.vB);
+            while (s < n_steps) {
+                const int jj = k / SPB, qq = k - jj * SPB;
+                const int row = (g + RG * jj) * R + qq * RS;      // first row of the slot within the CTA's rows
+                const int rc = min(RS, nrows_c - row);
+                mbar_wait(eb, phase ^ 1u, a.err);
+                mbar_arrive_expect_tx(fb, (uint32_t)rc * (uint32_t)row_bytes);
+                long long p = lo + row;
+                uint32_t dst = dst0;
+                int left = rc;
+                while (left > 0) {  // one copy unless the rows wrap around the shard end (or change worker)
+                    const RowRef ref = locate_row(a, mb, p);
+                    const int n = ref.room < (long long)left ? (int)ref.room : left;
+                    bulk_g2s(dst, ref.x, (uint32_t)n * (uint32_t)row_bytes, fb, pol);
+                    dst += (uint32_t)n * (uint32_t)row_bytes;
+                    left -= n;
+                    p += n;
+                }
+                phase ^= 1u;
+                k += nsg;
+                while (k >= nslg) {
+                    k -= nslg;
+                    ++s;
+                    mb = wrap(mb + a.vB);
+                }
+            }
+        }
+    } else if (warp >= NCW) {
+        // ======================================================================= exchange
+        if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
+        const int t = (warp - NCW) * 32 + lane;
+        bool xact[XC];
+        int col[XC];
+        double master[XC];
+        // accumulator values seen complete: `cur` belongs to this step's buffer, `oth` to the other one;
+        // they trade places every step (no dynamically indexed arrays: those would live in local memory)
+        const int b0 = (int)(a.xstep0 & 1);
+        unsigned long long pcur[XC], poth[XC], xcur[XC], xoth[XC], lcur = 0, loth = 0;
+        bool xsend[XC];   // this thread forwards the column's local total to the peers
+#pragma unroll
+        for (int i = 0; i < XC; ++i) {
+            const int tl = t + i * XT;
+            xact[i] = tl < fc;
+            col[i] = (int)crank * fc + tl;
+            master[i] = xact[i] ? a.model[col[i]] : 0.0;
+            pcur[i] = poth[i] = xcur[i] = xoth[i] = 0;
+            if (xact[i]) {
+                pcur[i] = a.gbase[(size_t)b0 * F + col[i]];
+                poth[i] = a.gbase[(size_t)(b0 ^ 1) * F + col[i]];
+                if (a.nranks > 1) {
+                    xcur[i] = a.gxbase[(size_t)b0 * F + col[i]];
+                    xoth[i] = a.gxbase[(size_t)(b0 ^ 1) * F + col[i]];
+                }
+            }
+            xsend[i] = a.nranks > 1 && xact[i] && (tl % a.ncl) == q;
+        }
+        const bool loss_lead = want_loss && crank == 0 && t == 0;   // sums the cluster's loss partials
+        const bool loss_root = loss_lead && q == 0;                 // writes loss_out
+        if (loss_root) { lcur = a.lbase[b0]; loth = a.lbase[b0 ^ 1]; }
+        const uint32_t wfull_a = smem_u32(wfull), wsm_a = smem_u32(wsm);
+
+        for (int s = 0; s < n_steps; ++s) {
+            const int b = (int)((a.xstep0 + s) & 1);
+            mbar_wait_cluster(smem_u32(rfull), (uint32_t)s & 1u, a.err);
+            if (t == 0) {
+                dbg_stamp(a, s, 6);
+                if (s + 1 < n_steps) mbar_arrive_expect_tx(smem_u32(rfull), recv_bytes);
+            }
+            long long T[XC];
+#pragma unroll
+            for (int i = 0; i < XC; ++i) {
+                T[i] = 0;
+                if (!xact[i]) continue;
+                long long P = 0;
+                bool bad = false;
+#pragma unroll
+                for (int k = 0; k < NSRC; ++k) {
+                    const float v = recv[k * fc + t + i * XT];
+                    bad = bad || !(fabsf(v) < a.part_limit);
+                    P += to_fix32(v);
+                }
+                if (bad) atomicCAS(a.err, 0, kErrRange);
+                red_add_u64(a.gacc + (size_t)b * F + col[i], ((unsigned long long)P << kClCntBits) + 1ull);
+            }
+            if (t == 0) dbg_stamp(a, s, 7);
+#pragma unroll
+            for (int i = 0; i < XC; ++i)
+                if (xact[i])
+                    T[i] = poll_total<false>(a.gacc + (size_t)b * F + col[i], pcur[i], (unsigned)a.ncl, a.err,
+                                             kErrTimeoutPart, kSpinLimit);
+            if (t == 0) dbg_stamp(a, s, 3);
+            if (a.nranks > 1) {
+                // this GPU's total of a column goes to every rank's accumulator; then wait for all ranks'
+#pragma unroll
+                for (int i = 0; i < XC; ++i) {
+                    if (!xsend[i]) continue;
+                    const unsigned long long val = ((unsigned long long)T[i] << kClCntBits) + 1ull;
+                    const size_t off = (size_t)b * F + col[i];
+                    if (a.mc_gx) {
+                        multimem_red_add_u64(a.mc_gx + off, val);
+                    } else {
+                        for (int p = 0; p < a.nranks; ++p) red_add_u64_sys(a.peer_gx[p] + off, val);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < XC; ++i)
+                    if (xact[i])
+                        T[i] = poll_total<true>(a.peer_gx[a.rank] + (size_t)b * F + col[i], xcur[i], (unsigned)a.nranks,
+                                                a.err, kErrTimeoutPeer, kPeerSpinLimit);
+            }
+#pragma unroll
+            for (int i = 0; i < XC; ++i) {
+                if (!xact[i]) continue;
+                master[i] -= a.eta_over_b * ((double)T[i] * kClFixInv);
+                if (s + 1 < n_steps) {
+                    const uint32_t wbits = __float_as_uint((float)master[i]);
+                    const uint32_t dsta = wsm_a + (uint32_t)(((s + 1) & 1) * F + col[i]) * 4u;
+#pragma unroll
+                    for (int d = 0; d < CS; ++d) st_async_b32(mapa_u32(dsta, (uint32_t)d), wbits, mapa_u32(wfull_a, (uint32_t)d));
+                }
+            }
+            if (t == 0) dbg_stamp(a, s, 4);
+            // ---- loss of step s: off the critical path; read back by the root one step late
+            if (loss_lead) {
+                const uint32_t lb = smem_u32(&lfull[s & 1]);
+                mbar_wait_cluster(lb, (uint32_t)(s >> 1) & 1u, a.err);
+                long long L = 0;
+#pragma unroll
+                for (int k = 0; k < NSRC; ++k) L += to_fix32(lrecv[(s & 1) * NSRC + k]);
+                if (s + 2 < n_steps) mbar_arrive_expect_tx(lb, (uint32_t)NSRC * 4u);
+                red_add_u64(a.lacc + b, ((unsigned long long)L << kClCntBits) + 1ull);
+                if (loss_root && s > 0) {
+                    const long long Lt = poll_total<false>(a.lacc + (b ^ 1), loth, (unsigned)a.ncl, a.err,
+                                                           kErrTimeoutPart, kSpinLimit);
+                    a.loss_out[s - 1] = ((double)Lt * kClFixInv) * a.inv_b;
+                }
+            }
+            // the other buffer is next step's
+#pragma unroll
+            for (int i = 0; i < XC; ++i) {
+                unsigned long long tmp = pcur[i]; pcur[i] = poth[i]; poth[i] = tmp;
+                tmp = xcur[i]; xcur[i] = xoth[i]; xoth[i] = tmp;
+            }
+            { const unsigned long long tmp = lcur; lcur = loth; loth = tmp; }
+        }
+        // after the loop `cur` is the buffer the NEXT step would use
+        const int bn = (int)((a.xstep0 + n_steps) & 1);
+        if (loss_root && n_steps > 0) {
+            const long long Lt = poll_total<false>(a.lacc + (bn ^ 1), loth, (unsigned)a.ncl, a.err, kErrTimeoutPart, kSpinLimit);
+            a.loss_out[n_steps - 1] = ((double)Lt * kClFixInv) * a.inv_b;
+            a.lbase[bn] = lcur;
+            a.lbase[bn ^ 1] = loth;
+        }
+        if (q == 0) {  // all clusters hold identical masters and saw identical accumulator values
+#pragma unroll
+            for (int i = 0; i < XC; ++i) {
+                if (!xact[i]) continue;
+                a.model[col[i]] = master[i];
+                a.gbase[(size_t)bn * F + col[i]] = pcur[i];
+                a.gbase[(size_t)(bn ^ 1) * F + col[i]] = poth[i];
+                if (a.nranks > 1) {
+                    a.gxbase[(size_t)bn * F + col[i]] = xcur[i];
+                    a.gxbase[(size_t)(bn ^ 1) * F + col[i]] = xoth[i];
+                }
+            }
+        }
+    } else {
+        // ======================================================================= compute
+        if (CREG > 0) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CREG > 0 ? CREG : 24));
+        const int rg = warp / WPG, wig = warp - rg * WPG;
+        const int gq = wig * 32 + lane;                 // float4 column chunk of this thread
+        const bool gv = gq * 4 < F;
+        const int ridx = row_of_lane<R>(lane);
+        const bool canon = lane == lane_of_row<R>(ridx);
+        unsigned char* const gring = ring + (size_t)rg * nsg * slot_bytes;
+        uint64_t* const gfullb = full + rg * nsg;
+        uint64_t* const gemptyb = empty + rg * nsg;
+        const uint32_t wsm_a = smem_u32(wsm);
+
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gv) {
+            const double* m = a.model + gq * 4;
+            w = make_float4((float)m[0], (float)m[1], (float)m[2], (float)m[3]);
+        }
+        // where this thread's gradient chunk goes: the owner CTA of its columns, one slot per (source CTA, group)
+        const int owner = gv ? (gq * 4) / fc : 0;
+        const uint32_t send_addr = mapa_u32(smem_u32(recv) + (uint32_t)((((int)crank * RG + rg) * fc + (gq * 4 - owner * fc)) * 4), (uint32_t)owner);
+        const uint32_t send_bar = mapa_u32(smem_u32(rfull), (uint32_t)owner);
+        const uint32_t lsend_bar0 = mapa_u32(smem_u32(&lfull[0]), 0u), lsend_bar1 = mapa_u32(smem_u32(&lfull[1]), 0u);
+        const uint32_t lsend_addr = mapa_u32(smem_u32(lrecv) + (uint32_t)(((int)crank * RG + rg) * 4), 0u);
+
+        uint32_t slot = 0, par = 0;  // this group's ring cursor
+        int red_buf = 0;
+        long long mb = mb0;
+        auto load_y = [&](long long mbs, int j) -> float {
+            const int i = j * R + ridx;
+            return (j < nst_c && i < nrows_c) ? __ldg(locate_row(a, mbs, lo + i).y) : 0.f;
+        };
+        float y_next = load_y(mb, rg);
+
+        for (int s = 0; s < n_steps; ++s) {
+            const long long mb_next = wrap(mb + a.vB);
+            float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+            float2* zyb = zy + (size_t)(s & 1) * a.zy_rows;
+            if (tid == 0) dbg_stamp(a, s, 0);
+            auto take_weights = [&]() {
+                mbar_wait_cluster(smem_u32(wfull), (uint32_t)(s - 1) & 1u, a.err);
+                if (tid == 0 && s + 1 < n_steps) mbar_arrive_expect_tx(smem_u32(wfull), (uint32_t)F * 4u);
+                if (gv) w = lds_v4(wsm_a + (uint32_t)((s & 1) * F + gq * 4) * 4u);
+            };
+            if (nsb == 0 && s > 0) take_weights();  // a CTA without rows still takes part in every exchange
+
+            for (int sb = 0; sb < nsb; ++sb) {
+                const int j = sb * RG + rg;               // this group's pass of the step
+                const bool have = j < nst_c;              // warp-uniform
+                const int rc = have ? min(R, nrows_c - j * R) : 0;
+                const float yv = y_next;
+                if (sb + 1 < nsb) y_next = load_y(mb, j + RG);
+                else y_next = (s + 1 < n_steps) ? load_y(mb_next, rg) : 0.f;
+                float4 x[R];
+#pragma unroll
+                for (int qq = 0; qq < SPB; ++qq) {
+                    if (qq * RS < rc) {  // warp-uniform
+                        mbar_wait(smem_u32(&gfullb[slot]), par, a.err);
+                        const uint32_t sbase = smem_u32(gring + (size_t)slot * slot_bytes);
+#pragma unroll
+                        for (int rr = 0; rr < RS; ++rr) {
+                            const int r = qq * RS + rr;
+                            x[r] = (gv && r < rc) ? lds_v4(sbase + (uint32_t)rr * (uint32_t)row_bytes + (uint32_t)gq * 16u)
+                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(&gemptyb[slot]));  // rows are in registers
+                        if (++slot == (uint32_t)nsg) { slot = 0; par ^= 1u; }
+                    } else {
+#pragma unroll
+                        for (int rr = 0; rr < RS; ++rr) x[qq * RS + rr] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
+                if (sb == 0 && s > 0) {
+                    // the rows of the step's first pass are already in registers: only now wait for the weights
+                    take_weights();
+                    if (tid == 0) dbg_stamp(a, s, 5);
+                }
+                float d[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    float acc = x[r].x * w.x;
+                    acc = fmaf(x[r].y, w.y, acc);
+                    acc = fmaf(x[r].z, w.z, acc);
+                    acc = fmaf(x[r].w, w.w, acc);
+                    d[r] = acc;
+                }
+                MultiReduce<R, 16>::run(d, lane);
+                float z = d[0];  // warp total for row ridx
+                if (WPG > 1) {
+                    float* rb = red + red_buf * (NCW * R);
+                    if (canon) rb[(rg * WPG + wig) * R + ridx] = z;
+                    named_bar_sync(2 + rg, CT);
+                    z = 0.f;
+#pragma unroll
+                    for (int k = 0; k < WPG; ++k) z += rb[(rg * WPG + k) * R + ridx];
+                    red_buf ^= 1;
+                }
+                float resid = 0.f;
+                if (ridx < rc) {
+                    resid = sigmoid_f(z) - yv;
+                    if (canon && wig == 0 && want_loss) zyb[j * R + ridx] = make_float2(z, yv);
+                }
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const float rr = __shfl_sync(0xffffffffu, resid, lane_of_row<R>(r));
+                    g.x = fmaf(rr, x[r].x, g.x);
+                    g.y = fmaf(rr, x[r].y, g.y);
+                    g.z = fmaf(rr, x[r].z, g.z);
+                    g.w = fmaf(rr, x[r].w, g.w);
+                }
+            }
+            if (tid == 0) dbg_stamp(a, s, 1);
+            // ---- hand the gradient chunk to the owner of its columns, straight from registers
+            if (gv) st_async_v4(send_addr, g, send_bar);
+            if (tid == 0) dbg_stamp(a, s, 2);
+            // ---- off the critical path: this group's loss of the step
+            if (wig == 0 && want_loss) {
+                float l = 0.f;
+                __syncwarp();
+                for (int sb = 0; sb < nsb; ++sb) {
+                    const int j = sb * RG + rg;
+                    for (int i = lane; i < R; i += 32) {
+                        if (j < nst_c && j * R + i < nrows_c) {
+                            const float2 v = zyb[j * R + i];
+                            l += row_loss_f(v.x, v.y);
+                        }
+                    }
+                }
+                l = warp_sum(l);
+                if (lane == 0)
+                    st_async_b32(lsend_addr + (uint32_t)((s & 1) * NSRC * 4), __float_as_uint(l), (s & 1) ? lsend_bar1 : lsend_bar0);
+            }
+            mb = mb_next;
+        }
+    }
+    // nobody leaves while a neighbour may still store into its shared memory
+    __syncwarp();
+    cluster_sync_all();
+}
+
+}  // namespace slk

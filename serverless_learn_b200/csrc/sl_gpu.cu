@@ -19,6 +19,7 @@
 #include "kernels.cuh"
 #include "kernels_wide.cuh"
 #include "kernels_multi.cuh"
+#include "kernels_cluster.cuh"
 
 namespace {
 
@@ -121,6 +122,24 @@ const Variant kVariants[] = {
 const int kAutoOrder[] = {1, 29, 22, 14, 11};  // measured best per width (tools/sweep.py, profiles/r1_summary.md)
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
+// ---- cluster kernel (K1c) variants ---------------------------------------------------
+struct ClVariant {
+    int wpg, rg, r, rs, cs, warps;
+    const void* fn;
+};
+#define SL_CLUSTER(WPG, RG, R, RS, CS, XW, CREG, XREG) \
+    ClVariant { WPG, RG, R, RS, CS, slk::cl_warps<WPG, RG, XW, CREG>(), \
+                (const void*)slk::lr_cluster_kernel<WPG, RG, R, RS, CS, XW, CREG, XREG> }
+const ClVariant kClVariants[] = {
+    SL_CLUSTER(8, 2, 16, 4, 8, 2, 104, 64),  // 1: F <= 1024, two row groups of 16 rows: a CTA's 32 rows of config 3 in
+                                             //    one pass; 20 warps, the compute warpgroups take 104 registers
+    SL_CLUSTER(8, 2, 8, 4, 8, 4, 0, 0),      // 2: F <= 1024, two row groups of 8 rows
+    SL_CLUSTER(8, 1, 16, 4, 8, 4, 0, 0),     // 3: F <= 1024, one row group (8 compute warps)
+    SL_CLUSTER(4, 4, 8, 4, 8, 4, 0, 0),      // 4: F <= 512, four row groups of 8 rows
+    SL_CLUSTER(8, 2, 16, 4, 8, 4, 0, 0),     // 5: as 1 without the register re-split (spills; for comparison)
+};
+constexpr int kNumClVariants = sizeof(kClVariants) / sizeof(kClVariants[0]);
+
 }  // namespace
 
 struct sl_handle {
@@ -145,6 +164,7 @@ struct sl_handle {
     int npart = 0;                       // >1 while sl_train_steps_multi runs: independent replicas, one grid partition each
     double* pmodel[8] = {};
     int vw = 0;                          // >1 while sl_train_steps_group runs: worker replicas trained as one job
+    bool forbid_simple = false;          // group / multi calls: the three-launch path has no multi-shard mode
     const float* vX[8] = {};
     const float* vy[8] = {};
     size_t shard_off = 0;                // 64 when the sealed stream starts with an sl_shard_header
@@ -168,6 +188,7 @@ struct sl_handle {
     size_t wmaster_bytes = 0;
     double* d_loss = nullptr;
     double* h_loss = nullptr;
+    double* h_loss_dev = nullptr;        // device alias of h_loss (mapped): K1c writes its losses straight there
     size_t loss_cap = 0;
     float *resid = nullptr, *rowloss = nullptr, *gpart = nullptr;
     double* gsum = nullptr;
@@ -195,6 +216,16 @@ struct sl_handle {
     int peer_n = 0, peer_rank = 0;       // 0 = not attached
     unsigned xflag_base = 0;
     long long opt_sync_path = 0;         // 0 auto (fused when attached), 1 NCCL per step
+    // cluster kernel (K1c)
+    unsigned long long* cl_scratch = nullptr;  // [gacc 2F][gbase 2F][gxbase 2F][lacc 2][lbase 2]
+    int cl_scratch_F = 0;
+    bool cl_dirty = false;               // a launch aborted: the accumulators are re-zeroed before the next one
+    long long cl_xstep = 0;              // steps taken through K1c so far (accumulator parity continues across launches)
+    int cl_max_clusters[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // per variant, for the shared-memory size in cl_smem_set
+    size_t cl_smem_set[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int cl_coop = -1;                    // cooperative + cluster launch accepted? (-1 = not tried)
+    long long opt_cl_variant = 0, opt_clusters = 0;
+    unsigned long long* mc_gx = nullptr; // multicast alias of the cross-GPU accumulators (sl_peer_attach_multicast)
 
     std::mutex mu;
     std::string err;
@@ -282,7 +313,12 @@ int ensure_loss_cap(sl_handle* h, size_t n) {
     size_t cap = std::max<size_t>(n, 1024);
     CK(h, cudaMalloc(&h->d_loss, sizeof(double) * cap));
     CK(h, cudaMalloc(&h->loss_fix, 8 * cap));
-    CK(h, cudaMallocHost(&h->h_loss, sizeof(double) * cap));
+    CK(h, cudaHostAlloc(&h->h_loss, sizeof(double) * cap, cudaHostAllocMapped));
+    h->h_loss_dev = nullptr;
+    if (cudaHostGetDevicePointer(&h->h_loss_dev, h->h_loss, 0) != cudaSuccess) {
+        cudaGetLastError();
+        h->h_loss_dev = nullptr;
+    }
     h->loss_cap = cap;
     return SL_OK;
 }
@@ -563,6 +599,228 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
     return SL_OK;
 }
 
+
+// ---- K1c: cluster kernel (kernels_cluster.cuh) -----------------------------------------
+struct ClusterPlan {
+    int variant = -1;  // index into kClVariants
+    int grid = 0, threads = 0;
+    slk::ClArgs args;
+    size_t smem = 0;
+};
+
+// Largest number of co-resident clusters of variant vi (one CTA per SM), cached on the handle.
+int cluster_capacity(sl_handle* h, int vi) {
+    if (h->cl_smem_set[vi] == h->smem_optin) return h->cl_max_clusters[vi];
+    const ClVariant& v = kClVariants[vi];
+    h->cl_max_clusters[vi] = 0;
+    h->cl_smem_set[vi] = h->smem_optin;
+    if (cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    if (v.cs > 8 && cudaFuncSetAttribute(v.fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(v.cs * h->num_sms));
+    cfg.blockDim = dim3((unsigned)(v.warps * 32));
+    cfg.dynamicSmemBytes = h->smem_optin;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)v.cs;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, v.fn, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;
+    }
+    h->cl_max_clusters[vi] = n;
+    return n;
+}
+
+// Returns false (with reason) when the cluster kernel cannot run this shape.
+bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
+    const int F = h->F;
+    if (h->npart > 1) { *why = "independent replicas run on the interleaved kernel"; return false; }
+    if (((uintptr_t)(h->shard + h->shard_off) & 15) != 0) { *why = "shard not 16-byte aligned"; return false; }
+    int vi = -1;
+    auto fits = [&](const ClVariant& v) { return F % (4 * v.cs) == 0 && F <= 128 * v.wpg && F / v.cs <= 128; };
+    if (h->opt_cl_variant > 0 && h->opt_cl_variant <= kNumClVariants) {
+        vi = (int)h->opt_cl_variant - 1;
+        if (!fits(kClVariants[vi])) { *why = "requested cluster variant does not hold this F"; return false; }
+    } else {
+        const int order[] = {F <= 512 ? 4 : 1, 1};
+        for (int k : order)
+            if (fits(kClVariants[k - 1])) { vi = k - 1; break; }
+        if (vi < 0) { *why = "F must be a multiple of 32 and at most 1024 for the cluster kernel"; return false; }
+    }
+    const ClVariant& v = kClVariants[vi];
+    int ncl = cluster_capacity(h, vi);
+    if (ncl < 1) { *why = "no cluster of this kernel fits on the device"; return false; }
+    if (h->opt_clusters > 0) ncl = (int)std::min<long long>(ncl, h->opt_clusters);
+    else if (h->opt_grid > 0) ncl = (int)std::max<long long>(1, std::min<long long>(ncl, h->opt_grid / v.cs));
+    ncl = std::min(ncl, (int)slk::kClCntMask);
+    slk::ClArgs& a = p->args;
+    memset(&a, 0, sizeof(a));
+    const long long Beff = (long long)h->B * (h->vw > 1 ? h->vw : 1);  // positions per step
+    const int grid = ncl * v.cs;
+    a.F = F;
+    a.B = (int)Beff;
+    a.vB = h->B;
+    a.nvw = h->vw > 1 ? h->vw : 0;
+    a.ncl = ncl;
+    a.fc = F / v.cs;
+    a.row_bytes = 4 * F;
+    a.zy_rows = (int)((((Beff + grid - 1) / grid + v.r - 1) / v.r) * v.r);
+    const int ncw = v.wpg * v.rg, nsrc = v.cs * v.rg;
+    const size_t recv_b = sizeof(float) * (size_t)nsrc * a.fc;
+    const size_t wsm_b = sizeof(float) * 2 * (size_t)F;
+    const size_t lrecv_b = sizeof(float) * 2 * (size_t)nsrc;
+    const size_t red_b = sizeof(float) * 2 * (size_t)ncw * v.r;
+    const size_t zy_b = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
+    const size_t slot_b = (size_t)v.rs * a.row_bytes;
+    const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + 8 * (2 * 32 + 4) + 512;
+    if (h->smem_optin < fixed + (size_t)v.rg * slot_b) { *why = "the ring does not fit in shared memory"; return false; }
+    size_t nsg = (h->smem_optin - fixed) / ((size_t)v.rg * slot_b);
+    nsg = std::min<size_t>(nsg, (size_t)(32 / v.rg));  // one producer lane per slot
+    if (h->opt_ring > 0) nsg = std::max<size_t>(1, std::min<size_t>(nsg, (size_t)h->opt_ring));
+    a.nsg = (int)nsg;
+    size_t off = (size_t)v.rg * nsg * slot_b;
+    off = align_up(off, 16); a.off_bar = (int)off;    off += 8 * (2 * (size_t)v.rg * nsg + 4);
+    off = align_up(off, 16); a.off_recv = (int)off;   off += recv_b;
+    off = align_up(off, 16); a.off_wsm = (int)off;    off += wsm_b;
+    off = align_up(off, 16); a.off_lrecv = (int)off;  off += lrecv_b;
+    off = align_up(off, 16); a.off_red = (int)off;    off += red_b;
+    off = align_up(off, 16); a.off_zy = (int)off;     off += zy_b;
+    if (off > h->smem_optin) { *why = "shared memory layout exceeds the SM"; return false; }
+    const int ranks = fused ? std::max(1, h->peer_n) : 1;
+    a.part_limit = 33554432.0f / (float)((long long)nsrc * ncl * ranks);  // 2^(63-6-32) over all adders
+    a.eta_over_b = h->eta / ((double)Beff * (double)ranks);
+    a.inv_b = 1.0 / (double)Beff;
+    p->smem = off;
+    p->variant = vi;
+    p->grid = grid;
+    p->threads = v.warps * 32;
+    return true;
+}
+
+size_t xblock_gx_offset(int F) { return sizeof(uint4) * 2 * 8 * (size_t)F + 8 * 3 * (size_t)F; }
+size_t xblock_bytes_for(int F) { return xblock_gx_offset(F) + 8 * 2 * (size_t)F; }
+
+// Enqueues the launches (events around them); the caller synchronises.  loss_dev: device-visible
+// array of n_steps doubles the kernel writes, or nullptr.
+int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss_dev, bool fused) {
+    const ClVariant& v = kClVariants[plan.variant];
+    const int F = h->F;
+    const size_t words = 6 * (size_t)F + 8;
+    if (!h->cl_scratch || h->cl_scratch_F != F) {
+        if (h->cl_scratch) cudaFree(h->cl_scratch);
+        h->cl_scratch = nullptr;
+        CK(h, cudaMalloc(&h->cl_scratch, 8 * words));
+        h->cl_scratch_F = F;
+        h->cl_dirty = true;
+    }
+    if (h->cl_dirty) {  // first use, or a launch gave up half way: start from zero (rare; costs a memset)
+        CK(h, cudaMemsetAsync(h->cl_scratch, 0, 8 * words, h->stream));
+        if (h->xblock) CK(h, cudaMemsetAsync(h->xblock + xblock_gx_offset(F), 0, 8 * 2 * (size_t)F, h->stream));
+        h->cl_dirty = false;
+    }
+    const int max_per_launch = h->opt_steps_per_launch > 0 ? (int)h->opt_steps_per_launch : kMaxStepsPerLaunch;
+    *h->h_err = 0;
+    unsigned long long* dbg = nullptr;
+    if (h->opt_dbg_step >= 0) {
+        const size_t dw = (size_t)4 * plan.grid * 16;
+        if (h->dbg_words < dw) {
+            if (h->dbg) cudaFree(h->dbg);
+            h->dbg = nullptr;
+            CK(h, cudaMalloc(&h->dbg, dw * 8));
+            h->dbg_words = dw;
+        }
+        CK(h, cudaMemsetAsync(h->dbg, 0, dw * 8, h->stream));
+        dbg = h->dbg;
+    }
+    CK(h, cudaEventRecord(h->ev0, h->stream));
+    int done = 0;
+    while (done < n_steps) {
+        const int n = std::min(max_per_launch, n_steps - done);
+        slk::ClArgs a = plan.args;
+        a.X = reinterpret_cast<const float*>(h->shard + h->shard_off);
+        a.y = a.X + (size_t)h->n_rows * F;
+        a.n_rows = h->n_rows;
+        a.step0 = h->step;
+        a.n_steps = n;
+        a.model = h->model;
+        a.gacc = h->cl_scratch;
+        a.gbase = h->cl_scratch + 2 * (size_t)F;
+        a.gxbase = h->cl_scratch + 4 * (size_t)F;
+        a.lacc = h->cl_scratch + 6 * (size_t)F;
+        a.lbase = a.lacc + 2;
+        a.loss_out = loss_dev ? loss_dev + done : nullptr;
+        a.xstep0 = h->cl_xstep;
+        a.err = h->d_err;
+        for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; }
+        if (fused) {
+            a.nranks = h->peer_n;
+            a.rank = h->peer_rank;
+            for (int p = 0; p < h->peer_n; ++p)
+                a.peer_gx[p] = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(h->peer_base[p]) + xblock_gx_offset(F));
+            a.mc_gx = h->mc_gx;
+        }
+        a.dbg = done == 0 ? dbg : nullptr;
+        a.dbg_step = done == 0 && dbg ? (int)h->opt_dbg_step : 0;
+        void* params[] = {&a};
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3((unsigned)plan.grid);
+        cfg.blockDim = dim3((unsigned)plan.threads);
+        cfg.dynamicSmemBytes = plan.smem;
+        cfg.stream = h->stream;
+        cudaLaunchAttribute at[2];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)v.cs;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        at[1].id = cudaLaunchAttributeCooperative;
+        at[1].val.cooperative = 1;
+        cfg.attrs = at;
+        // the clusters wait for one another: ask for a co-resident grid where the driver takes both attributes
+        cudaError_t e = cudaErrorUnknown;
+        if (h->cl_coop != 0) {
+            cfg.numAttrs = 2;
+            e = cudaLaunchKernelExC(&cfg, v.fn, params);
+            if (h->cl_coop < 0) {
+                h->cl_coop = e == cudaSuccess ? 1 : 0;
+                if (e != cudaSuccess) cudaGetLastError();
+            }
+        }
+        if (h->cl_coop == 0) {
+            cfg.numAttrs = 1;
+            e = cudaLaunchKernelExC(&cfg, v.fn, params);
+        }
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(h, SL_ECUDA, "cluster kernel launch failed: %s", cudaGetErrorString(e));
+        }
+        h->launches++;
+        h->k1_launches++;
+        h->step += n;
+        h->cl_xstep += n;
+        done += n;
+    }
+    CK(h, cudaEventRecord(h->ev1, h->stream));
+    h->path_used = fused ? 7 : 6;
+    h->variant_used = 100 + plan.variant + 1;
+    h->grid_used = plan.grid;
+    h->ns_used = plan.args.nsg;
+    h->smem_used = (long long)plan.smem;
+    return SL_OK;
+}
+
 // one step of the simple path; sync != 0 adds the all-reduce between finish and apply
 int launch_simple_step(sl_handle* h, double* d_loss_slot, bool sync) {
     const float* X = reinterpret_cast<const float*>(h->shard + h->shard_off);
@@ -714,6 +972,45 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     const size_t nloss = (size_t)n_steps * (h->npart > 1 ? h->npart : 1);  // one loss per step and replica
     int rc = ensure_loss_cap(h, nloss);
     if (rc) return rc;
+    // K1c: narrow rows as thread-block clusters (one replica, or one group job; fused across GPUs when
+    // peers are attached).  "variant" selects among the older kernels, so it is only taken when unset.
+    if ((h->opt_path == 0 || h->opt_path == 6) && h->opt_variant == 0 && h->npart <= 1 &&
+        (!sync || (h->peer_n > 0 && h->opt_sync_path == 0))) {
+        ClusterPlan cp;
+        std::string cwhy;
+        if (plan_cluster(h, &cp, &cwhy, sync)) {
+            const bool nccl_loss = sync && loss_out && h->comm && h->nranks > 1 && g_nccl.AllReduce;
+            double* loss_dev = nullptr;
+            if (loss_out) loss_dev = (nccl_loss || !h->h_loss_dev) ? h->d_loss : h->h_loss_dev;
+            rc = run_cluster(h, cp, n_steps, loss_dev, sync);
+            if (rc) return rc;
+            if (nccl_loss) {  // each rank evaluated the loss of its own rows: mean over ranks
+                int nrc = g_nccl.AllReduce(h->d_loss, h->d_loss, (size_t)n_steps, kNcclFloat64, kNcclSum, h->comm, h->stream);
+                if (nrc != 0) return fail(h, SL_ENCCL, "ncclAllReduce(loss) failed (%d)", nrc);
+                slk::scale_kernel<<<(n_steps + 255) / 256, 256, 0, h->stream>>>(h->d_loss, n_steps, 1.0 / (double)h->nranks);
+                h->launches++;
+            }
+            if (loss_out && loss_dev == h->d_loss)
+                CK(h, cudaMemcpyAsync(h->h_loss, h->d_loss, sizeof(double) * nloss, cudaMemcpyDeviceToHost, h->stream));
+            CK(h, cudaStreamSynchronize(h->stream));
+            CK(h, cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
+            if (*h->h_err != 0) {
+                const int code = *h->h_err;
+                *h->h_err = 0;
+                if (code == slk::kErrRange)
+                    return fail(h, SL_EINVAL, "a gradient partial left the fixed-point range (|sum| must stay below %g per "
+                                "row group and step): features too large for this kernel, the model is not usable",
+                                (double)cp.args.part_limit);
+                h->cl_dirty = true;
+                return fail(h, SL_ETIMEOUT, "in-kernel wait timed out (watchdog code %d)", code);
+            }
+            if (loss_out) memcpy(loss_out, h->h_loss, sizeof(double) * nloss);
+            return SL_OK;
+        }
+        if (h->opt_path == 6) return fail(h, SL_EINVAL, "cluster kernel requested but unavailable: %s", cwhy.c_str());
+    } else if (h->opt_path == 6) {
+        return fail(h, SL_EINVAL, "cluster kernel requested but this call cannot use it (variant set, replicas, or NCCL path)");
+    }
     if (!sync && interleaved_ok(h)) {  // independent replicas, interleaved on every SM
         CK(h, cudaEventRecord(h->ev0, h->stream));
         rc = run_interleaved(h, n_steps, loss_out != nullptr);
@@ -739,7 +1036,7 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
         const Variant& v = kVariants[plan.variant];
         fused = v.xb && (h->F + plan.args.xslice - 1) / plan.args.xslice <= plan.grid && h->peer_n <= 8;
     }
-    if (!sync && h->opt_path == 1 && !persist)
+    if (!sync && (h->opt_path == 1 || h->forbid_simple) && !persist)
         return fail(h, SL_EINVAL, "persistent path requested but unavailable: %s", why.c_str());
     if (sync && !fused && (!h->comm || !g_nccl.AllReduce))
         return fail(h, SL_ESTATE, "the fused peer path cannot run this shape (%s) and no NCCL communicator "
@@ -862,6 +1159,7 @@ int sl_destroy(sl_handle* h) {
     cudaFree(h->model); cudaFree(h->old); cudaFree(h->shard); cudaFree(h->in_buf);
     cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->w32buf); cudaFree(h->d_loss); cudaFree(h->loss_fix);
     cudaFree(h->dbg);
+    cudaFree(h->cl_scratch);
     for (int p = 0; p < h->peer_n; ++p)
         if (p != h->peer_rank && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
     cudaFree(h->xblock);
@@ -909,6 +1207,8 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "debug_skip_compute") h->opt_dbg_skip = value;
     else if (k == "tma_chunk") h->opt_tma_chunk = value;
     else if (k == "sync_path") h->opt_sync_path = value;
+    else if (k == "cl_variant") h->opt_cl_variant = value;
+    else if (k == "clusters") h->opt_clusters = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
 }
@@ -932,6 +1232,7 @@ long long sl_get_info(sl_handle* h, const char* key) {
     if (k == "nranks") return h->nranks;
     if (k == "peers") return h->peer_n;
     if (k == "num_variants") return kNumVariants;
+    if (k == "num_cl_variants") return kNumClVariants;
     return SL_EINVAL;
 }
 
@@ -1186,11 +1487,10 @@ int sl_train_steps_group(sl_handle* const* handles, int W, int n_steps, double* 
         h->vy[k] = h->vX[k] + (size_t)handles[k]->n_rows * h->F;
     }
     h->vw = W;
-    const long long saved_path = h->opt_path;
-    if (h->opt_path == 0) h->opt_path = 1;  // the simple path has no multi-shard mode: fail instead of falling back
-    int rc = h->opt_path == 1 ? train_impl(h, n_steps, loss_out, false)
-                              : fail(h, SL_EINVAL, "sl_train_steps_group runs on the persistent kernel only");
-    h->opt_path = saved_path;
+    h->forbid_simple = true;  // the simple path has no multi-shard mode: fail instead of falling back
+    int rc = h->opt_path != 2 ? train_impl(h, n_steps, loss_out, false)
+                              : fail(h, SL_EINVAL, "sl_train_steps_group runs on the persistent kernels only");
+    h->forbid_simple = false;
     h->vw = 0;
     if (rc) return rc;
     for (int k = 1; k < W; ++k) {  // every replica leaves with the new model (old is untouched, as in sl_train_steps)
@@ -1234,11 +1534,10 @@ int sl_train_steps_multi(sl_handle* const* handles, int W, int n_steps, double* 
         h->pmodel[k] = handles[k]->model;
     }
     h->npart = W;
-    const long long saved_path = h->opt_path;
-    if (h->opt_path == 0) h->opt_path = 1;
-    int rc = h->opt_path == 1 ? train_impl(h, n_steps, loss_out, false)
-                              : fail(h, SL_EINVAL, "sl_train_steps_multi runs on the persistent kernel only");
-    h->opt_path = saved_path;
+    h->forbid_simple = true;
+    int rc = (h->opt_path == 0 || h->opt_path == 1) ? train_impl(h, n_steps, loss_out, false)
+                                                    : fail(h, SL_EINVAL, "sl_train_steps_multi runs on the persistent kernel only");
+    h->forbid_simple = false;
     h->npart = 0;
     if (rc) return rc;
     for (int k = 1; k < W; ++k) handles[k]->step = h->step;
@@ -1406,7 +1705,7 @@ int sl_peer_export(sl_handle* h, void* handle64) {
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard dg(h->device);
     if (!h->xblock) {
-        const size_t bytes = sizeof(uint4) * 2 * 8 * (size_t)h->F + 8 * 3 * (size_t)h->F;
+        const size_t bytes = xblock_bytes_for(h->F);  // inboxes and totals of K1/K1w, then K1c's accumulators
         CK(h, cudaMalloc(&h->xblock, bytes));
         CK(h, cudaMemset(h->xblock, 0, bytes));
         h->xblock_bytes = bytes;

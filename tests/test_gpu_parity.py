@@ -276,7 +276,7 @@ def test_lr_config_c3_shape_64_steps(sl, orc):
         r.shard_synth(n)
         lg = r.train_steps(steps)
         wg = r.model()
-        assert r.info("path") == 1
+        assert r.info("path") == 6          # the cluster kernel is the default for narrow rows
     assert w_err(wg, w) <= W_TOL
     assert float(np.max(np.abs(lg - lo) / lo)) <= L_TOL
     assert lg[-1] < lg[0]
@@ -346,7 +346,8 @@ def test_sync_mode_single_rank_equals_local_steps(sl, orc):
         assert w_err(r.model(), w) <= W_TOL
 
 
-def test_fused_sync_path_single_rank(sl, orc):
+@pytest.mark.parametrize("path", [1, 6])
+def test_fused_sync_path_single_rank(sl, orc, path):
     # the in-kernel cross-GPU stage with nranks = 1 (no peer): owner slices, second counter
     # and the load of the all-rank total are all exercised; numbers must equal plain steps
     n, F, B, steps, eta = 900, 1024, 96, 11, 0.2
@@ -358,17 +359,20 @@ def test_fused_sync_path_single_rank(sl, orc):
         r.peer_export()
         r.peer_attach(1, 0, b"")
         assert r.info("peers") == 1
+        r.set_option("path", path)
         lg = np.concatenate([r.train_steps_sync(4), r.train_steps_sync(steps - 4)])
-        assert r.info("path") == 4
+        assert r.info("path") == (4 if path == 1 else 7)
         assert w_err(r.model(), w) <= W_TOL
         assert float(np.max(np.abs(lg - lo) / lo)) <= L_TOL
     with sl.Replica(F, B, eta=eta) as r2:              # bit-identical to the single-GPU kernel
         r2.load_shard(X, y)
+        r2.set_option("path", path)
         r2.train_steps(steps)
         with sl.Replica(F, B, eta=eta) as r3:
             r3.load_shard(X, y)
             r3.peer_export()
             r3.peer_attach(1, 0, b"")
+            r3.set_option("path", path)
             r3.train_steps_sync(steps)
             assert np.array_equal(r2.model(), r3.model())
 
@@ -509,7 +513,7 @@ def test_group_of_workers_on_one_gpu_equals_sync_loop(sl, orc, W, n, F, B, varia
             r.load_shard(X, y)
         reps[0].set_option("variant", variant)
         lg = np.concatenate([sl.Replica.train_steps_group(reps, 4), sl.Replica.train_steps_group(reps, steps - 4)])
-        assert reps[0].info("path") == 1
+        assert reps[0].info("path") == (6 if variant == 0 and F % 32 == 0 and F <= 1024 else 1)
         for r in reps:
             assert np.array_equal(r.model(), reps[0].model())        # every replica leaves with the new model
             assert r.info("step") == steps
@@ -616,6 +620,7 @@ def test_multi_replicas_on_one_gpu_take_local_steps(sl, orc, W, n, F, B, variant
                 solo.load_shard(*shards[k])
                 solo.set_option("variant", variant)
                 solo.set_option("grid", grid)
+                solo.set_option("path", 1)
                 ls = solo.train_steps(steps)
                 if path == 1 or F == 1024:      # same arithmetic as the solo kernel: bit for bit
                     assert np.array_equal(solo.model(), r.model()) and np.array_equal(ls, lg[k]), k

@@ -1,0 +1,73 @@
+"""Time the cluster kernel (K1c) over its variants, cluster counts and call lengths; optional per-step timeline.
+    python tools/k1c_bench.py [--F 1024 --B 4096 --rows 1048576 --steps 2048] [--clv 1,2,3] [--clusters 0] [--timeline]
+Timeline points (globaltimer ns): P0 step start, P5 weights taken, P1 compute done, P2 gradient sent (compute thread 0);
+P6 partials landed, P7 red issued, P3 total seen, P4 weights broadcast (exchange thread 0)."""
+import argparse
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from serverless_learn_b200 import Replica, SlError  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--F", type=int, default=1024)
+ap.add_argument("--B", type=int, default=4096)
+ap.add_argument("--rows", type=int, default=1 << 20)
+ap.add_argument("--steps", default="2048")
+ap.add_argument("--clv", default="1,2,3")
+ap.add_argument("--clusters", default="0")
+ap.add_argument("--ring", type=int, default=0)
+ap.add_argument("--loss", type=int, default=1)
+ap.add_argument("--path", type=int, default=6)
+ap.add_argument("--timeline", action="store_true")
+a = ap.parse_args()
+peak = 6535.7
+algo = 4 * (a.F + 1) * a.B + 16 * a.F
+names = ["P0 step start", "P1 compute done", "P2 gradient sent", "P3 total seen", "P4 weights broadcast",
+         "P5 weights taken", "P6 partials landed", "P7 red issued"]
+order = [0, 5, 1, 2, 6, 7, 3, 4]
+with Replica(a.F, a.B) as r:
+    r.shard_synth(a.rows)
+    r.set_option("path", a.path)
+    for clv in [int(x) for x in a.clv.split(",")]:
+        for ncl in [int(x) for x in a.clusters.split(",")]:
+            for steps in [int(x) for x in a.steps.split(",")]:
+                r.set_option("cl_variant", clv); r.set_option("clusters", ncl); r.set_option("ring_slots", a.ring)
+                r.set_option("debug_timeline", -1)
+                try:
+                    r.train_steps(64, want_loss=bool(a.loss))
+                    ts = []
+                    for _ in range(5):
+                        r.train_steps(steps, want_loss=bool(a.loss))
+                        ts.append(r.last_train_ms())
+                    us = float(np.median(ts)) * 1e3 / steps
+                    print(f"clv={clv} grid={r.info('grid')} slots={r.info('ring_slots')} steps={steps} "
+                          f"{us:8.3f} us/step (min {min(ts) * 1e3 / steps:.3f})  {algo / us / 1e3:8.1f} GB/s  "
+                          f"frac={algo / us / 1e3 / peak:.3f}", flush=True)
+                except SlError as e:
+                    print(f"clv={clv} clusters={ncl}: {e}", flush=True)
+                    continue
+            if a.timeline:
+                r.set_option("debug_timeline", 10)
+                r.train_steps(32, want_loss=bool(a.loss))
+                G = r.info("grid")
+                buf = np.zeros(4 * G * 16, dtype=np.uint64)
+                assert r._L.sl_debug_read(r._h, buf.ctypes.data_as(C.POINTER(C.c_ulonglong)), buf.size) == 0
+                t = buf.reshape(4, G, 8, 2).astype(np.int64)
+                for s in range(1, 3):
+                    g0 = t[s, :, 0, 1].min()
+                    print(f"--- clv={clv} step {10 + s}: globaltimer ns after the earliest CTA's step start (min / median / max over CTAs)")
+                    for p in order:
+                        if not t[s, :, p, 1].any():
+                            continue
+                        v = t[s, :, p, 1] - g0
+                        print(f"  {names[p]:22s} {v.min():7d} {int(np.median(v)):7d} {v.max():7d}")
+                    ck = t[s, :, :, 0]
+                    print("  SM-clock deltas (median over CTAs): " + ", ".join(
+                        f"{names[b_][:2]}-{names[a_][:2]}={int(np.median(ck[:, b_] - ck[:, a_]))}"
+                        for a_, b_ in [(0, 5), (5, 1), (1, 2), (6, 7), (7, 3), (3, 4)]))
+                    nxt = t[s + 1, :, 0, 1] - g0
+                    print(f"  next step start        {nxt.min():7d} {int(np.median(nxt)):7d} {nxt.max():7d}")
