@@ -10,7 +10,7 @@
 //      (st.async, completion counted in bytes on the owner's mbarrier) — no staging, no barrier;
 //   2. ONE hop through L2 between the clusters: the owner converts every partial to fixed point, adds
 //      the integers and adds the cluster's sum into a global accumulator with a single red.add.u64 whose
-//      low bits count arrivals ((sum << 6) + 1).  Readers poll the accumulator itself until the count
+//      low bits count arrivals ((sum << 7) + 1).  Readers poll the accumulator itself until the count
 //      says every cluster has added: data and "flag" are one word, so there is no release fence and no
 //      separate counter.  Accumulators are never cleared: a reader subtracts the value it saw complete
 //      two steps earlier (two buffers, by step parity), arithmetic mod 2^64;
@@ -32,7 +32,7 @@
 
 namespace slk {
 
-constexpr int kClCntBits = 6;                                  // arrivals per word: up to 63 adders
+constexpr int kClCntBits = 7;                                  // arrivals per word: up to 127 adders
 constexpr unsigned long long kClCntMask = (1ull << kClCntBits) - 1ull;
 constexpr double kClFixInv = 1.0 / 4294967296.0;               // fixed point: 2^-32 units
 constexpr int kErrRange = 5;                                   // a gradient partial left the fixed-point range
@@ -46,7 +46,7 @@ struct ClArgs {
     long long step0;       // global step index of the first step of this launch
     int n_steps;
     double* model;         // fp64 master weights [F] (model_state, src/master.cc:58)
-    unsigned long long* gacc;    // [2][F] gradient accumulators: (sum << 6) + arrivals, never cleared
+    unsigned long long* gacc;    // [2][F] gradient accumulators: (sum << 7) + arrivals, never cleared
     unsigned long long* gbase;   // [2][F] their values when the previous launch ended
     unsigned long long* lacc;    // [2]    loss accumulators, same encoding
     unsigned long long* lbase;   // [2]
@@ -67,7 +67,8 @@ struct ClArgs {
     int nsg;               // ring slots per row group
     int row_bytes;         // 4*F
     int zy_rows;
-    int off_bar, off_recv, off_wsm, off_lrecv, off_red, off_zy;  // smem offsets
+    int ycap;              // label slots per row group and step (>= passes per group * R)
+    int off_bar, off_recv, off_wsm, off_lrecv, off_red, off_zy, off_yb;  // smem offsets
     unsigned long long* dbg;
     int dbg_step;
     // several worker replicas on ONE GPU trained as one job (sl_train_steps_group), as in LrArgs
@@ -138,6 +139,21 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned 
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void cp_async_4(uint32_t dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// diagnostics: 16 (clock64, globaltimer) pairs per CTA and step, [4 steps][grid][32]
+__device__ __forceinline__ void cl_stamp(const ClArgs& a, int s, int point) {
+    if (a.dbg != nullptr && s >= a.dbg_step && s < a.dbg_step + 4) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        unsigned long long* d = a.dbg + ((size_t)(s - a.dbg_step) * gridDim.x + blockIdx.x) * 32;
+        d[2 * point] = (unsigned long long)clock64();
+        d[2 * point + 1] = t;
+    }
+}
 // exact: scaling by 2^32 does not round in fp32, the conversion rounds once
 __device__ __forceinline__ long long to_fix32(float v) { return __float2ll_rn(v * 4294967296.0f); }
 
@@ -170,10 +186,11 @@ constexpr int cl_warps() {
 template <int WPG, int RG, int R, int RS, int CS, int XW, int CREG, int XREG>
 __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_cluster_kernel(const ClArgs a) {
     static_assert(R % RS == 0, "a pass is a whole number of ring slots");
+    static_assert(WPG > 1, "the labels become visible at the row group's barrier");
     static_assert(CREG == 0 || (WPG * RG) % 4 == 0, "register re-split needs whole compute warpgroups");
     constexpr int NCW = WPG * RG;     // compute warps
     constexpr int XT = XW * 32;       // exchange threads
-    constexpr int XC = (128 + XT - 1) / XT;  // owned columns per exchange thread
+    constexpr int XC = (1024 / CS + XT - 1) / XT;  // owned columns per exchange thread (F <= 1024)
     constexpr int SPB = R / RS;       // ring slots per pass
     constexpr int NSRC = CS * RG;     // gradient partials an owner receives per step
     constexpr int CT = WPG * 32;      // threads of a row group
@@ -196,6 +213,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
     float* lrecv = reinterpret_cast<float*>(smem + a.off_lrecv);        // [2][NSRC]
     float* red = reinterpret_cast<float*>(smem + a.off_red);            // [2][NCW][R]
     float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);            // [2][zy_rows]
+    float* ybuf = reinterpret_cast<float*>(smem + a.off_yb);            // [2][RG][ycap] labels of a step's rows
 
     const uint32_t slot_bytes = (uint32_t)RS * (uint32_t)row_bytes;
     const long long lo = ((long long)c * a.B) / G;
@@ -321,7 +339,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
             const int b = (int)((a.xstep0 + s) & 1);
             mbar_wait_cluster(smem_u32(rfull), (uint32_t)s & 1u, a.err);
             if (t == 0) {
-                dbg_stamp(a, s, 6);
+                cl_stamp(a, s, 6);
                 if (s + 1 < n_steps) mbar_arrive_expect_tx(smem_u32(rfull), recv_bytes);
             }
             long long T[XC];
@@ -340,13 +358,13 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                 if (bad) atomicCAS(a.err, 0, kErrRange);
                 red_add_u64(a.gacc + (size_t)b * F + col[i], ((unsigned long long)P << kClCntBits) + 1ull);
             }
-            if (t == 0) dbg_stamp(a, s, 7);
+            if (t == 0) cl_stamp(a, s, 7);
 #pragma unroll
             for (int i = 0; i < XC; ++i)
                 if (xact[i])
                     T[i] = poll_total<false>(a.gacc + (size_t)b * F + col[i], pcur[i], (unsigned)a.ncl, a.err,
                                              kErrTimeoutPart, kSpinLimit);
-            if (t == 0) dbg_stamp(a, s, 3);
+            if (t == 0) cl_stamp(a, s, 3);
             if (a.nranks > 1) {
                 // this GPU's total of a column goes to every rank's accumulator; then wait for all ranks'
 #pragma unroll
@@ -366,18 +384,28 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                         T[i] = poll_total<true>(a.peer_gx[a.rank] + (size_t)b * F + col[i], xcur[i], (unsigned)a.nranks,
                                                 a.err, kErrTimeoutPeer, kPeerSpinLimit);
             }
+            // new fp32 weights to every CTA of the cluster, 16 bytes per store: the four lanes of a quad hold
+            // four consecutive columns; each gathers the quad's values and serves a quarter of the CTAs
 #pragma unroll
             for (int i = 0; i < XC; ++i) {
-                if (!xact[i]) continue;
-                master[i] -= a.eta_over_b * ((double)T[i] * kClFixInv);
-                if (s + 1 < n_steps) {
-                    const uint32_t wbits = __float_as_uint((float)master[i]);
-                    const uint32_t dsta = wsm_a + (uint32_t)(((s + 1) & 1) * F + col[i]) * 4u;
+                if (xact[i]) master[i] -= a.eta_over_b * ((double)T[i] * kClFixInv);
+                const float wv = (float)master[i];
+                const int qb = lane & ~3;
+                float4 w4;
+                w4.x = __shfl_sync(0xffffffffu, wv, qb);
+                w4.y = __shfl_sync(0xffffffffu, wv, qb + 1);
+                w4.z = __shfl_sync(0xffffffffu, wv, qb + 2);
+                w4.w = __shfl_sync(0xffffffffu, wv, qb + 3);
+                if (xact[i] && s + 1 < n_steps) {
+                    const uint32_t dsta = wsm_a + (uint32_t)(((s + 1) & 1) * F + (col[i] & ~3)) * 4u;
 #pragma unroll
-                    for (int d = 0; d < CS; ++d) st_async_b32(mapa_u32(dsta, (uint32_t)d), wbits, mapa_u32(wfull_a, (uint32_t)d));
+                    for (int d0 = 0; d0 < CS; d0 += 4) {
+                        const int d = d0 + (lane & 3);
+                        if (d < CS) st_async_v4(mapa_u32(dsta, (uint32_t)d), w4, mapa_u32(wfull_a, (uint32_t)d));
+                    }
                 }
             }
-            if (t == 0) dbg_stamp(a, s, 4);
+            if (t == 0) cl_stamp(a, s, 4);
             // ---- loss of step s: off the critical path; read back by the root one step late
             if (loss_lead) {
                 const uint32_t lb = smem_u32(&lfull[s & 1]);
@@ -450,17 +478,26 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
         uint32_t slot = 0, par = 0;  // this group's ring cursor
         int red_buf = 0;
         long long mb = mb0;
-        auto load_y = [&](long long mbs, int j) -> float {
-            const int i = j * R + ridx;
-            return (j < nst_c && i < nrows_c) ? __ldg(locate_row(a, mbs, lo + i).y) : 0.f;
+        // Labels: a global load inside a pass would put an HBM round trip into every pass.  Instead the group
+        // copies the labels of a whole step into shared memory (cp.async, no registers) one step ahead, right
+        // after handing off the gradient; they become visible at the first pass's barrier.
+        const int ct = wig * 32 + lane;
+        auto stage_labels = [&](long long mbs, int buf) {
+            float* dst = ybuf + (size_t)(buf * RG + rg) * a.ycap;
+            for (int u = ct; u < nsb * R; u += CT) {
+                const int sbi = u / R, i = u - sbi * R;
+                const int j = sbi * RG + rg, ic = j * R + i;
+                if (j < nst_c && ic < nrows_c) cp_async_4(smem_u32(dst + u), locate_row(a, mbs, lo + ic).y);
+            }
+            cp_async_commit();
         };
-        float y_next = load_y(mb, rg);
+        if (n_steps > 0) stage_labels(mb, 0);
 
         for (int s = 0; s < n_steps; ++s) {
             const long long mb_next = wrap(mb + a.vB);
             float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
             float2* zyb = zy + (size_t)(s & 1) * a.zy_rows;
-            if (tid == 0) dbg_stamp(a, s, 0);
+            if (tid == 0) cl_stamp(a, s, 0);
             auto take_weights = [&]() {
                 mbar_wait_cluster(smem_u32(wfull), (uint32_t)(s - 1) & 1u, a.err);
                 if (tid == 0 && s + 1 < n_steps) mbar_arrive_expect_tx(smem_u32(wfull), (uint32_t)F * 4u);
@@ -472,9 +509,6 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                 const int j = sb * RG + rg;               // this group's pass of the step
                 const bool have = j < nst_c;              // warp-uniform
                 const int rc = have ? min(R, nrows_c - j * R) : 0;
-                const float yv = y_next;
-                if (sb + 1 < nsb) y_next = load_y(mb, j + RG);
-                else y_next = (s + 1 < n_steps) ? load_y(mb_next, rg) : 0.f;
                 float4 x[R];
 #pragma unroll
                 for (int qq = 0; qq < SPB; ++qq) {
@@ -495,10 +529,11 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                         for (int rr = 0; rr < RS; ++rr) x[qq * RS + rr] = make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                 }
+                if (tid == 0 && sb == 1) cl_stamp(a, s, 12);
                 if (sb == 0 && s > 0) {
                     // the rows of the step's first pass are already in registers: only now wait for the weights
                     take_weights();
-                    if (tid == 0) dbg_stamp(a, s, 5);
+                    if (tid == 0) cl_stamp(a, s, 5);
                 }
                 float d[R];
 #pragma unroll
@@ -511,20 +546,25 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                 }
                 MultiReduce<R, 16>::run(d, lane);
                 float z = d[0];  // warp total for row ridx
+                if (tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 8 : 13);
                 if (WPG > 1) {
                     float* rb = red + red_buf * (NCW * R);
                     if (canon) rb[(rg * WPG + wig) * R + ridx] = z;
+                    if (sb == 0) cp_async_wait_all();  // this thread's share of the step's labels has landed
                     named_bar_sync(2 + rg, CT);
                     z = 0.f;
 #pragma unroll
                     for (int k = 0; k < WPG; ++k) z += rb[(rg * WPG + k) * R + ridx];
                     red_buf ^= 1;
                 }
+                if (tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 9 : 14);
                 float resid = 0.f;
                 if (ridx < rc) {
+                    const float yv = ybuf[(size_t)((s & 1) * RG + rg) * a.ycap + sb * R + ridx];
                     resid = sigmoid_f(z) - yv;
                     if (canon && wig == 0 && want_loss) zyb[j * R + ridx] = make_float2(z, yv);
                 }
+                if (tid == 0 && sb == 0) cl_stamp(a, s, 10);
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     const float rr = __shfl_sync(0xffffffffu, resid, lane_of_row<R>(r));
@@ -533,11 +573,12 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                     g.z = fmaf(rr, x[r].z, g.z);
                     g.w = fmaf(rr, x[r].w, g.w);
                 }
+                if (tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 11 : 15);
             }
-            if (tid == 0) dbg_stamp(a, s, 1);
+            if (tid == 0) cl_stamp(a, s, 1);
             // ---- hand the gradient chunk to the owner of its columns, straight from registers
             if (gv) st_async_v4(send_addr, g, send_bar);
-            if (tid == 0) dbg_stamp(a, s, 2);
+            if (tid == 0) cl_stamp(a, s, 2);
             // ---- off the critical path: this group's loss of the step
             if (wig == 0 && want_loss) {
                 float l = 0.f;
@@ -555,6 +596,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                 if (lane == 0)
                     st_async_b32(lsend_addr + (uint32_t)((s & 1) * NSRC * 4), __float_as_uint(l), (s & 1) ? lsend_bar1 : lsend_bar0);
             }
+            if (s + 1 < n_steps) stage_labels(mb_next, (s + 1) & 1);
             mb = mb_next;
         }
     }

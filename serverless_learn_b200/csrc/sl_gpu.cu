@@ -136,7 +136,10 @@ const ClVariant kClVariants[] = {
     SL_CLUSTER(8, 2, 8, 4, 8, 4, 0, 0),      // 2: F <= 1024, two row groups of 8 rows
     SL_CLUSTER(8, 1, 16, 4, 8, 4, 0, 0),     // 3: F <= 1024, one row group (8 compute warps)
     SL_CLUSTER(4, 4, 8, 4, 8, 4, 0, 0),      // 4: F <= 512, four row groups of 8 rows
-    SL_CLUSTER(8, 2, 16, 4, 8, 4, 0, 0),     // 5: as 1 without the register re-split (spills; for comparison)
+    SL_CLUSTER(8, 2, 16, 4, 4, 2, 104, 64),  // 5: as 1 in clusters of 4 (more SMs take part where 8 do not tile the GPCs)
+    SL_CLUSTER(8, 2, 8, 4, 4, 4, 0, 0),      // 6: as 2 in clusters of 4
+    SL_CLUSTER(8, 1, 16, 4, 4, 4, 0, 0),     // 7: as 3 in clusters of 4
+    SL_CLUSTER(8, 2, 16, 4, 2, 2, 104, 64),  // 8: as 1 in clusters of 2
 };
 constexpr int kNumClVariants = sizeof(kClVariants) / sizeof(kClVariants[0]);
 
@@ -221,8 +224,8 @@ struct sl_handle {
     int cl_scratch_F = 0;
     bool cl_dirty = false;               // a launch aborted: the accumulators are re-zeroed before the next one
     long long cl_xstep = 0;              // steps taken through K1c so far (accumulator parity continues across launches)
-    int cl_max_clusters[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // per variant, for the shared-memory size in cl_smem_set
-    size_t cl_smem_set[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int cl_max_clusters[16] = {};        // per variant, for the shared-memory size in cl_smem_set
+    size_t cl_smem_set[16] = {};
     int cl_coop = -1;                    // cooperative + cluster launch accepted? (-1 = not tried)
     long long opt_cl_variant = 0, opt_clusters = 0;
     unsigned long long* mc_gx = nullptr; // multicast alias of the cross-GPU accumulators (sl_peer_attach_multicast)
@@ -649,7 +652,7 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     if (h->npart > 1) { *why = "independent replicas run on the interleaved kernel"; return false; }
     if (((uintptr_t)(h->shard + h->shard_off) & 15) != 0) { *why = "shard not 16-byte aligned"; return false; }
     int vi = -1;
-    auto fits = [&](const ClVariant& v) { return F % (4 * v.cs) == 0 && F <= 128 * v.wpg && F / v.cs <= 128; };
+    auto fits = [&](const ClVariant& v) { return F % (4 * v.cs) == 0 && F <= 128 * v.wpg; };
     if (h->opt_cl_variant > 0 && h->opt_cl_variant <= kNumClVariants) {
         vi = (int)h->opt_cl_variant - 1;
         if (!fits(kClVariants[vi])) { *why = "requested cluster variant does not hold this F"; return false; }
@@ -683,8 +686,10 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     const size_t lrecv_b = sizeof(float) * 2 * (size_t)nsrc;
     const size_t red_b = sizeof(float) * 2 * (size_t)ncw * v.r;
     const size_t zy_b = sizeof(float) * 2 * 2 * (size_t)a.zy_rows;
+    a.ycap = (a.zy_rows / v.r + v.rg - 1) / v.rg * v.r;  // passes per row group * R
+    const size_t yb_b = sizeof(float) * 2 * (size_t)v.rg * a.ycap;
     const size_t slot_b = (size_t)v.rs * a.row_bytes;
-    const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + 8 * (2 * 32 + 4) + 512;
+    const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + yb_b + 8 * (2 * 32 + 4) + 512;
     if (h->smem_optin < fixed + (size_t)v.rg * slot_b) { *why = "the ring does not fit in shared memory"; return false; }
     size_t nsg = (h->smem_optin - fixed) / ((size_t)v.rg * slot_b);
     nsg = std::min<size_t>(nsg, (size_t)(32 / v.rg));  // one producer lane per slot
@@ -697,9 +702,10 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     off = align_up(off, 16); a.off_lrecv = (int)off;  off += lrecv_b;
     off = align_up(off, 16); a.off_red = (int)off;    off += red_b;
     off = align_up(off, 16); a.off_zy = (int)off;     off += zy_b;
+    off = align_up(off, 16); a.off_yb = (int)off;     off += yb_b;
     if (off > h->smem_optin) { *why = "shared memory layout exceeds the SM"; return false; }
     const int ranks = fused ? std::max(1, h->peer_n) : 1;
-    a.part_limit = 33554432.0f / (float)((long long)nsrc * ncl * ranks);  // 2^(63-6-32) over all adders
+    a.part_limit = 16777216.0f / (float)((long long)nsrc * ncl * ranks);  // 2^(63-7-32) over all adders
     a.eta_over_b = h->eta / ((double)Beff * (double)ranks);
     a.inv_b = 1.0 / (double)Beff;
     p->smem = off;
@@ -734,7 +740,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
     *h->h_err = 0;
     unsigned long long* dbg = nullptr;
     if (h->opt_dbg_step >= 0) {
-        const size_t dw = (size_t)4 * plan.grid * 16;
+        const size_t dw = (size_t)4 * plan.grid * 32;  // K1c stamps 16 points
         if (h->dbg_words < dw) {
             if (h->dbg) cudaFree(h->dbg);
             h->dbg = nullptr;

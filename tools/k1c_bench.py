@@ -27,8 +27,10 @@ a = ap.parse_args()
 peak = 6535.7
 algo = 4 * (a.F + 1) * a.B + 16 * a.F
 names = ["P0 step start", "P1 compute done", "P2 gradient sent", "P3 total seen", "P4 weights broadcast",
-         "P5 weights taken", "P6 partials landed", "P7 red issued"]
-order = [0, 5, 1, 2, 6, 7, 3, 4]
+         "P5 weights taken", "P6 partials landed", "P7 red issued", "P8 pass0 dots reduced", "P9 pass0 barrier+sum",
+         "P10 pass0 sigmoid", "P11 pass0 gradient", "P12 pass1 rows loaded", "P13 pass1 dots reduced",
+         "P14 pass1 barrier+sum", "P15 pass1 gradient"]
+order = [0, 5, 8, 9, 10, 11, 12, 13, 14, 15, 1, 2, 6, 7, 3, 4]
 with Replica(a.F, a.B) as r:
     r.shard_synth(a.rows)
     r.set_option("path", a.path)
@@ -54,9 +56,9 @@ with Replica(a.F, a.B) as r:
                 r.set_option("debug_timeline", 10)
                 r.train_steps(32, want_loss=bool(a.loss))
                 G = r.info("grid")
-                buf = np.zeros(4 * G * 16, dtype=np.uint64)
+                buf = np.zeros(4 * G * 32, dtype=np.uint64)
                 assert r._L.sl_debug_read(r._h, buf.ctypes.data_as(C.POINTER(C.c_ulonglong)), buf.size) == 0
-                t = buf.reshape(4, G, 8, 2).astype(np.int64)
+                t = buf.reshape(4, G, 16, 2).astype(np.int64)
                 for s in range(1, 3):
                     g0 = t[s, :, 0, 1].min()
                     print(f"--- clv={clv} step {10 + s}: globaltimer ns after the earliest CTA's step start (min / median / max over CTAs)")
@@ -68,6 +70,6 @@ with Replica(a.F, a.B) as r:
                     ck = t[s, :, :, 0]
                     print("  SM-clock deltas (median over CTAs): " + ", ".join(
                         f"{names[b_][:2]}-{names[a_][:2]}={int(np.median(ck[:, b_] - ck[:, a_]))}"
-                        for a_, b_ in [(0, 5), (5, 1), (1, 2), (6, 7), (7, 3), (3, 4)]))
+                        for a_, b_ in [(0, 5), (5, 8), (8, 9), (9, 10), (10, 11), (11, 12), (12, 13), (13, 14), (14, 15), (5, 1), (1, 2), (6, 7), (7, 3), (3, 4)]))
                     nxt = t[s + 1, :, 0, 1] - g0
                     print(f"  next step start        {nxt.min():7d} {int(np.median(nxt)):7d} {nxt.max():7d}")
