@@ -48,8 +48,8 @@ struct ClArgs {
     double* model;         // fp64 master weights [F] (model_state, src/master.cc:58)
     unsigned long long* gacc;    // [2][F] gradient accumulators: (sum << 7) + arrivals, never cleared
     unsigned long long* gbase;   // [2][F] their values when the previous launch ended
-    unsigned long long* lacc;    // [2]    loss accumulators, same encoding
-    unsigned long long* lbase;   // [2]
+    unsigned long long* lacc;    // [3]    loss accumulators, same encoding, by step mod 3
+    unsigned long long* lbase;   // [3]
     double* loss_out;      // device [n_steps]: mean loss of every step, written by the kernel; or nullptr
     long long xstep0;      // accumulator parity of this launch's first step (continues across launches)
     // same-box data parallel: one kernel per GPU, totals summed through peer-mapped memory
@@ -60,6 +60,7 @@ struct ClArgs {
     double eta_over_b;     // eta / (B * ranks)
     double inv_b;          // 1 / B
     float part_limit;      // |partial| above this could overflow the accumulator word
+    int poll_delay, poll_gap;  // SM cycles before the first look at an accumulator / between looks
     int* err;              // 0 = ok; set by the watchdog
     // geometry, computed on the host
     int ncl;               // clusters in the grid
@@ -68,7 +69,7 @@ struct ClArgs {
     int row_bytes;         // 4*F
     int zy_rows;
     int ycap;              // label slots per row group and step (>= passes per group * R)
-    int off_bar, off_recv, off_wsm, off_lrecv, off_red, off_zy, off_yb;  // smem offsets
+    int off_bar, off_recv, off_wsm, off_lrecv, off_red, off_zy, off_yb, off_prev;  // smem offsets
     unsigned long long* dbg;
     int dbg_step;
     // several worker replicas on ONE GPU trained as one job (sl_train_steps_group), as in LrArgs
@@ -144,7 +145,11 @@ __device__ __forceinline__ void cp_async_4(uint32_t dst, const void* src) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-// diagnostics: 16 (clock64, globaltimer) pairs per CTA and step, [4 steps][grid][32]
+// diagnostics: 16 (clock64, globaltimer) pairs per CTA and step, [4 steps][grid][32].  Points 8..15 sit inside
+// the passes and perturb them (0.2 us per step at config 3): compiled in only with -DSL_CL_FINE_STAMPS=1.
+#ifndef SL_CL_FINE_STAMPS
+#define SL_CL_FINE_STAMPS 0
+#endif
 __device__ __forceinline__ void cl_stamp(const ClArgs& a, int s, int point) {
     if (a.dbg != nullptr && s >= a.dbg_step && s < a.dbg_step + 4) {
         unsigned long long t;
@@ -174,17 +179,62 @@ __device__ __forceinline__ long long poll_total(const unsigned long long* p, uns
 }
 
 // Warps of a CTA: compute, exchange, one producer, padded to whole warpgroups when registers are re-split.
-template <int WPG, int RG, int XW, int CREG>
+template <int WPG, int RG, int XW, int CREG, int PW>
 constexpr int cl_warps() {
-    return CREG > 0 ? (WPG * RG + XW + 1 + 3) / 4 * 4 : WPG * RG + XW + 1;
+    return CREG > 0 ? (WPG * RG + XW + PW + 3) / 4 * 4 : WPG * RG + XW + PW;
+}
+
+// The same for the XC columns of one exchange thread at once: every round issues all outstanding loads
+// before it looks at any of them, so the columns' L2 round trips overlap.  Polls compete with the adders for
+// the accumulators' L2 lines (four staggered loads in flight per column made the hop 1.5x SLOWER), so the
+// first look waits `delay` cycles and later ones `gap` cycles.
+template <bool SYS, int XC>
+__device__ __forceinline__ void poll_totals(unsigned long long* const (&p)[XC], const bool (&act)[XC],
+                                            unsigned long long (&prev)[XC], long long (&T)[XC], unsigned want,
+                                            int delay, int gap, int* err, int code, uint32_t limit) {
+    bool done[XC];
+#pragma unroll
+    for (int i = 0; i < XC; ++i) done[i] = !act[i];
+    if (delay > 0) {
+        const long long t0 = clock64();
+        while (clock64() - t0 < delay) {}
+    }
+    uint32_t spins = 0;
+    for (;;) {
+        unsigned long long v[XC];
+#pragma unroll
+        for (int i = 0; i < XC; ++i)
+            if (!done[i]) v[i] = SYS ? ld_relaxed_sys_u64(p[i]) : ld_relaxed_u64(p[i]);
+        bool all = true;
+#pragma unroll
+        for (int i = 0; i < XC; ++i) {
+            if (done[i]) continue;
+            const unsigned long long d = v[i] - prev[i];
+            if ((d & kClCntMask) == (unsigned long long)want) {
+                done[i] = true;
+                prev[i] = v[i];
+                T[i] = (long long)(d - (unsigned long long)want) >> kClCntBits;  // exact: the low bits are zero now
+            } else {
+                all = false;
+            }
+        }
+        if (all) break;
+        if (spin_abort(spins, err, code, limit)) break;
+        if (gap > 0) {
+            const long long t0 = clock64();
+            while (clock64() - t0 < gap) {}
+        }
+    }
 }
 
 // WPG warps cover a row (one float4 column chunk per thread: F <= 128*WPG); RG row groups of WPG warps
 // take R rows each per pass, from their own ring of RS-row slots; CS = CTAs per cluster; XW exchange
 // warps share the (at most 128) columns this CTA owns.  CREG > 0: the compute warpgroups take CREG
-// registers per thread from the exchange / producer warps (setmaxnreg), which keep XREG.
-template <int WPG, int RG, int R, int RS, int CS, int XW, int CREG, int XREG>
-__global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_cluster_kernel(const ClArgs a) {
+// registers per thread from the exchange / producer warps (setmaxnreg), which keep XREG.  PW = 1: a warp of
+// its own issues the TMA row copies; PW = 0: lanes of the first exchange warp do, once per step after the
+// weights have gone out (for shapes where a step is one pass: a slot is then always free when it is asked for).
+template <int WPG, int RG, int R, int RS, int CS, int XW, int CREG, int XREG, int PW>
+__global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_cluster_kernel(const ClArgs a) {
     static_assert(R % RS == 0, "a pass is a whole number of ring slots");
     static_assert(WPG > 1, "the labels become visible at the row group's barrier");
     static_assert(CREG == 0 || (WPG * RG) % 4 == 0, "register re-split needs whole compute warpgroups");
@@ -208,12 +258,14 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
     uint64_t* rfull = empty + RG * nsg;                                  // gradient partials of a step landed
     uint64_t* wfull = rfull + 1;                                         // next step's weights landed
     uint64_t* lfull = wfull + 1;                                         // [2] loss partials of a step landed
+    uint64_t* xdone = lfull + 2;                                         // the exchange warps have read this step's partials
     float* recv = reinterpret_cast<float*>(smem + a.off_recv);          // [NSRC][fc]
     float* wsm = reinterpret_cast<float*>(smem + a.off_wsm);            // [2][F]
     float* lrecv = reinterpret_cast<float*>(smem + a.off_lrecv);        // [2][NSRC]
     float* red = reinterpret_cast<float*>(smem + a.off_red);            // [2][NCW][R]
     float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);            // [2][zy_rows]
     float* ybuf = reinterpret_cast<float*>(smem + a.off_yb);            // [2][RG][ycap] labels of a step's rows
+    unsigned long long* xprev = reinterpret_cast<unsigned long long*>(smem + a.off_prev);  // [4][fc] accumulator values seen complete
 
     const uint32_t slot_bytes = (uint32_t)RS * (uint32_t)row_bytes;
     const long long lo = ((long long)c * a.B) / G;
@@ -240,6 +292,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
         mbar_init(smem_u32(wfull), 1);
         mbar_init(smem_u32(&lfull[0]), 1);
         mbar_init(smem_u32(&lfull[1]), 1);
+        mbar_init(smem_u32(xdone), XW);
         fence_mbar_init();
         // what the first phases will receive (later phases are armed by their waiters)
         if (n_steps > 0) mbar_arrive_expect_tx(smem_u32(rfull), recv_bytes);
@@ -252,55 +305,68 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
     __syncthreads();
     cluster_sync_all();  // every CTA's barriers exist before anybody stores into a neighbour
 
-    // Register re-split (warpgroup-uniform: the compute warps fill whole warpgroups): every role states its
-    // budget at the top of its own branch.
-    if (warp > NCW + XW) {
-        // padding warp of the last warpgroup: nothing to do
-        if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
-    } else if (warp == NCW + XW) {
-        // ======================================================================= producer
-        if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
-        // Lane l owns ring slot l % nsg of row group l / nsg and fetches that slot's uses over the whole
-        // launch (issuing a slot costs a thread several hundred cycles; one lane would bound the step).
-        const int g = lane / nsg, sl = lane - g * nsg;
-        // slots of one step that belong to group g: passes g, g+RG, ... of SPB slots, the last maybe short
-        int nslg = 0;
-        if (g < RG)
-            for (int j = g; j < nst_c; j += RG) nslg += (min(R, nrows_c - j * R) + RS - 1) / RS;
-        if (g < RG && nslg > 0) {
-            const uint64_t pol = policy_evict_first();
-            const uint32_t eb = smem_u32(&empty[g * nsg + sl]), fb = smem_u32(&full[g * nsg + sl]);
-            const uint32_t dst0 = smem_u32(ring + ((size_t)g * nsg + sl) * slot_bytes);
-            int s = sl / nslg, k = sl - s * nslg;  // step and slot-of-step of this lane's next use
-            uint32_t phase = 0;
-            long long mb = mb0;
-            for (int i = 0; i < s && i < n_steps; ++i) mb = wrap(mb + a.vB);
-            while (s < n_steps) {
-                const int jj = k / SPB, qq = k - jj * SPB;
-                const int row = (g + RG * jj) * R + qq * RS;      // first row of the slot within the CTA's rows
-                const int rc = min(RS, nrows_c - row);
-                mbar_wait(eb, phase ^ 1u, a.err);
-                mbar_arrive_expect_tx(fb, (uint32_t)rc * (uint32_t)row_bytes);
-                long long p = lo + row;
-                uint32_t dst = dst0;
-                int left = rc;
-                while (left > 0) {  // one copy unless the rows wrap around the shard end (or change worker)
-                    const RowRef ref = locate_row(a, mb, p);
-                    const int n = ref.room < (long long)left ? (int)ref.room : left;
-                    bulk_g2s(dst, ref.x, (uint32_t)n * (uint32_t)row_bytes, fb, pol);
-                    dst += (uint32_t)n * (uint32_t)row_bytes;
-                    left -= n;
-                    p += n;
-                }
-                phase ^= 1u;
-                k += nsg;
-                while (k >= nslg) {
-                    k -= nslg;
-                    ++s;
-                    mb = wrap(mb + a.vB);
-                }
+    // ---- TMA producer: lane l owns ring slot l % nsg of row group l / nsg and fetches that slot's uses over the
+    // whole launch (issuing a slot costs a thread several hundred cycles; one lane would bound the step)
+    const bool prod_warp = PW ? warp == NCW + XW : warp == NCW;
+    int pr_g = 0, pr_sl = 0, pr_nslg = 0, pr_s = n_steps, pr_k = 0, pr_prev = -1;
+    uint32_t pr_phase = 0, pr_eb = 0, pr_fb = 0, pr_dst0 = 0;
+    long long pr_mb = mb0;
+    uint64_t pr_pol = 0;
+    if (prod_warp) {
+        pr_g = lane / nsg;
+        pr_sl = lane - pr_g * nsg;
+        // slots of one step that belong to the group: passes g, g+RG, ... of SPB slots, the last maybe short
+        if (pr_g < RG)
+            for (int j = pr_g; j < nst_c; j += RG) pr_nslg += (min(R, nrows_c - j * R) + RS - 1) / RS;
+        if (pr_g < RG && pr_nslg > 0) {
+            pr_pol = policy_evict_first();
+            pr_eb = smem_u32(&empty[pr_g * nsg + pr_sl]);
+            pr_fb = smem_u32(&full[pr_g * nsg + pr_sl]);
+            pr_dst0 = smem_u32(ring + ((size_t)pr_g * nsg + pr_sl) * slot_bytes);
+            pr_s = pr_sl / pr_nslg;           // step and slot-of-step of this lane's next use
+            pr_k = pr_sl - pr_s * pr_nslg;
+            for (int i = 0; i < pr_s && i < n_steps; ++i) pr_mb = wrap(pr_mb + a.vB);
+        }
+    }
+    // issues this lane's uses, in order, as long as the slot's previous use lies at a step <= max_prev
+    auto produce = [&](int max_prev) {
+        while (pr_s < n_steps && pr_prev <= max_prev) {
+            const int jj = pr_k / SPB, qq = pr_k - jj * SPB;
+            const int row = (pr_g + RG * jj) * R + qq * RS;      // first row of the slot within the CTA's rows
+            const int rc = min(RS, nrows_c - row);
+            mbar_wait(pr_eb, pr_phase ^ 1u, a.err);
+            mbar_arrive_expect_tx(pr_fb, (uint32_t)rc * (uint32_t)row_bytes);
+            long long p = lo + row;
+            uint32_t dst = pr_dst0;
+            int left = rc;
+            while (left > 0) {  // one copy unless the rows wrap around the shard end (or change worker)
+                const RowRef ref = locate_row(a, pr_mb, p);
+                const int n = ref.room < (long long)left ? (int)ref.room : left;
+                bulk_g2s(dst, ref.x, (uint32_t)n * (uint32_t)row_bytes, pr_fb, pr_pol);
+                dst += (uint32_t)n * (uint32_t)row_bytes;
+                left -= n;
+                p += n;
+            }
+            pr_phase ^= 1u;
+            pr_prev = pr_s;
+            pr_k += nsg;
+            while (pr_k >= pr_nslg) {
+                pr_k -= pr_nslg;
+                ++pr_s;
+                pr_mb = wrap(pr_mb + a.vB);
             }
         }
+    };
+
+    // Register re-split (warpgroup-uniform: the compute warps fill whole warpgroups): every role states its
+    // budget at the top of its own branch.
+    if (warp >= NCW + XW + PW) {
+        // padding warp of the last warpgroup: nothing to do
+        if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
+    } else if (PW && warp == NCW + XW) {
+        // ======================================================================= producer
+        if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
+        produce(0x7fffffff);
     } else if (warp >= NCW) {
         // ======================================================================= exchange
         if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
@@ -308,10 +374,8 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
         bool xact[XC];
         int col[XC];
         double master[XC];
-        // accumulator values seen complete: `cur` belongs to this step's buffer, `oth` to the other one;
-        // they trade places every step (no dynamically indexed arrays: those would live in local memory)
-        const int b0 = (int)(a.xstep0 & 1);
-        unsigned long long pcur[XC], poth[XC], xcur[XC], xoth[XC], lcur = 0, loth = 0;
+        // accumulator values seen complete live in shared memory, one private slot per thread, column and
+        // buffer ([local b=0,1][cross-GPU b=0,1]): registers are what the compute warps need
         bool xsend[XC];   // this thread forwards the column's local total to the peers
 #pragma unroll
         for (int i = 0; i < XC; ++i) {
@@ -319,21 +383,21 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
             xact[i] = tl < fc;
             col[i] = (int)crank * fc + tl;
             master[i] = xact[i] ? a.model[col[i]] : 0.0;
-            pcur[i] = poth[i] = xcur[i] = xoth[i] = 0;
             if (xact[i]) {
-                pcur[i] = a.gbase[(size_t)b0 * F + col[i]];
-                poth[i] = a.gbase[(size_t)(b0 ^ 1) * F + col[i]];
+                xprev[0 * fc + tl] = a.gbase[col[i]];
+                xprev[1 * fc + tl] = a.gbase[F + col[i]];
                 if (a.nranks > 1) {
-                    xcur[i] = a.gxbase[(size_t)b0 * F + col[i]];
-                    xoth[i] = a.gxbase[(size_t)(b0 ^ 1) * F + col[i]];
+                    xprev[2 * fc + tl] = a.gxbase[col[i]];
+                    xprev[3 * fc + tl] = a.gxbase[F + col[i]];
                 }
             }
             xsend[i] = a.nranks > 1 && xact[i] && (tl % a.ncl) == q;
         }
-        const bool loss_lead = want_loss && crank == 0 && t == 0;   // sums the cluster's loss partials
-        const bool loss_root = loss_lead && q == 0;                 // writes loss_out
-        if (loss_root) { lcur = a.lbase[b0]; loth = a.lbase[b0 ^ 1]; }
         const uint32_t wfull_a = smem_u32(wfull), wsm_a = smem_u32(wsm);
+        if (!PW && warp == NCW) {  // first use of every ring slot
+            produce(-1);
+            __syncwarp();
+        }
 
         for (int s = 0; s < n_steps; ++s) {
             const int b = (int)((a.xstep0 + s) & 1);
@@ -342,33 +406,52 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                 cl_stamp(a, s, 6);
                 if (s + 1 < n_steps) mbar_arrive_expect_tx(smem_u32(rfull), recv_bytes);
             }
-            long long T[XC];
+            // the cluster's sum of every owned column: all partials are read and converted before the first
+            // red goes out (the asm statements keep their order; plain loads may not move across them)
+            long long T[XC], P[XC];
+            bool bad = false;
 #pragma unroll
             for (int i = 0; i < XC; ++i) {
                 T[i] = 0;
+                P[i] = 0;
                 if (!xact[i]) continue;
-                long long P = 0;
-                bool bad = false;
+                // the cluster's partials of a column are summed in a fixed pairwise order (every cluster, every
+                // GPU does the same), then converted once: integers from here on
+                float v[NSRC];
 #pragma unroll
-                for (int k = 0; k < NSRC; ++k) {
-                    const float v = recv[k * fc + t + i * XT];
-                    bad = bad || !(fabsf(v) < a.part_limit);
-                    P += to_fix32(v);
-                }
-                if (bad) atomicCAS(a.err, 0, kErrRange);
-                red_add_u64(a.gacc + (size_t)b * F + col[i], ((unsigned long long)P << kClCntBits) + 1ull);
+                for (int k = 0; k < NSRC; ++k) v[k] = recv[k * fc + t + i * XT];
+#pragma unroll
+                for (int w = 1; w < NSRC; w *= 2)
+#pragma unroll
+                    for (int k = 0; k + w < NSRC; k += 2 * w) v[k] += v[k + w];
+                bad = bad || !(fabsf(v[0]) < a.part_limit);
+                P[i] = to_fix32(v[0]);
             }
+            unsigned long long* gp[XC];
+            unsigned long long pv[XC];
+#pragma unroll
+            for (int i = 0; i < XC; ++i) {
+                gp[i] = a.gacc + (size_t)b * F + col[i];
+                pv[i] = xact[i] ? xprev[b * fc + t + i * XT] : 0ull;
+                if (xact[i]) red_add_u64(gp[i], ((unsigned long long)P[i] << kClCntBits) + 1ull);
+            }
+            // the compute warps hold back their next burst of shared-memory loads (pulling the next step's rows
+            // into registers) until the partials have been read: the two would queue in the same pipe
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(xdone));
+            if (bad) atomicCAS(a.err, 0, kErrRange);
             if (t == 0) cl_stamp(a, s, 7);
+            poll_totals<false, XC>(gp, xact, pv, T, (unsigned)a.ncl, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPart, kSpinLimit);
 #pragma unroll
             for (int i = 0; i < XC; ++i)
-                if (xact[i])
-                    T[i] = poll_total<false>(a.gacc + (size_t)b * F + col[i], pcur[i], (unsigned)a.ncl, a.err,
-                                             kErrTimeoutPart, kSpinLimit);
+                if (xact[i]) xprev[b * fc + t + i * XT] = pv[i];
             if (t == 0) cl_stamp(a, s, 3);
             if (a.nranks > 1) {
                 // this GPU's total of a column goes to every rank's accumulator; then wait for all ranks'
 #pragma unroll
                 for (int i = 0; i < XC; ++i) {
+                    gp[i] = a.peer_gx[a.rank] + (size_t)b * F + col[i];
+                    pv[i] = xact[i] ? xprev[(2 + b) * fc + t + i * XT] : 0ull;
                     if (!xsend[i]) continue;
                     const unsigned long long val = ((unsigned long long)T[i] << kClCntBits) + 1ull;
                     const size_t off = (size_t)b * F + col[i];
@@ -378,11 +461,10 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                         for (int p = 0; p < a.nranks; ++p) red_add_u64_sys(a.peer_gx[p] + off, val);
                     }
                 }
+                poll_totals<true, XC>(gp, xact, pv, T, (unsigned)a.nranks, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPeer, kPeerSpinLimit);
 #pragma unroll
                 for (int i = 0; i < XC; ++i)
-                    if (xact[i])
-                        T[i] = poll_total<true>(a.peer_gx[a.rank] + (size_t)b * F + col[i], xcur[i], (unsigned)a.nranks,
-                                                a.err, kErrTimeoutPeer, kPeerSpinLimit);
+                    if (xact[i]) xprev[(2 + b) * fc + t + i * XT] = pv[i];
             }
             // new fp32 weights to every CTA of the cluster, 16 bytes per store: the four lanes of a quad hold
             // four consecutive columns; each gathers the quad's values and serves a quarter of the CTAs
@@ -406,47 +488,24 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                 }
             }
             if (t == 0) cl_stamp(a, s, 4);
-            // ---- loss of step s: off the critical path; read back by the root one step late
-            if (loss_lead) {
-                const uint32_t lb = smem_u32(&lfull[s & 1]);
-                mbar_wait_cluster(lb, (uint32_t)(s >> 1) & 1u, a.err);
-                long long L = 0;
-#pragma unroll
-                for (int k = 0; k < NSRC; ++k) L += to_fix32(lrecv[(s & 1) * NSRC + k]);
-                if (s + 2 < n_steps) mbar_arrive_expect_tx(lb, (uint32_t)NSRC * 4u);
-                red_add_u64(a.lacc + b, ((unsigned long long)L << kClCntBits) + 1ull);
-                if (loss_root && s > 0) {
-                    const long long Lt = poll_total<false>(a.lacc + (b ^ 1), loth, (unsigned)a.ncl, a.err,
-                                                           kErrTimeoutPart, kSpinLimit);
-                    a.loss_out[s - 1] = ((double)Lt * kClFixInv) * a.inv_b;
-                }
+            if (!PW && warp == NCW) {
+                // refill the slots whose previous use is consumed by now: the rows of step s+1 went into registers
+                // right after this step's partials had been read
+                produce(s + 1);
+                __syncwarp();
             }
-            // the other buffer is next step's
-#pragma unroll
-            for (int i = 0; i < XC; ++i) {
-                unsigned long long tmp = pcur[i]; pcur[i] = poth[i]; poth[i] = tmp;
-                tmp = xcur[i]; xcur[i] = xoth[i]; xoth[i] = tmp;
-            }
-            { const unsigned long long tmp = lcur; lcur = loth; loth = tmp; }
-        }
-        // after the loop `cur` is the buffer the NEXT step would use
-        const int bn = (int)((a.xstep0 + n_steps) & 1);
-        if (loss_root && n_steps > 0) {
-            const long long Lt = poll_total<false>(a.lacc + (bn ^ 1), loth, (unsigned)a.ncl, a.err, kErrTimeoutPart, kSpinLimit);
-            a.loss_out[n_steps - 1] = ((double)Lt * kClFixInv) * a.inv_b;
-            a.lbase[bn] = lcur;
-            a.lbase[bn ^ 1] = loth;
         }
         if (q == 0) {  // all clusters hold identical masters and saw identical accumulator values
 #pragma unroll
             for (int i = 0; i < XC; ++i) {
                 if (!xact[i]) continue;
                 a.model[col[i]] = master[i];
-                a.gbase[(size_t)bn * F + col[i]] = pcur[i];
-                a.gbase[(size_t)(bn ^ 1) * F + col[i]] = poth[i];
+                const int tl = t + i * XT;
+                a.gbase[col[i]] = xprev[0 * fc + tl];
+                a.gbase[F + col[i]] = xprev[1 * fc + tl];
                 if (a.nranks > 1) {
-                    a.gxbase[(size_t)bn * F + col[i]] = xcur[i];
-                    a.gxbase[(size_t)(bn ^ 1) * F + col[i]] = xoth[i];
+                    a.gxbase[col[i]] = xprev[2 * fc + tl];
+                    a.gxbase[F + col[i]] = xprev[3 * fc + tl];
                 }
             }
         }
@@ -475,6 +534,10 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
         const uint32_t lsend_bar0 = mapa_u32(smem_u32(&lfull[0]), 0u), lsend_bar1 = mapa_u32(smem_u32(&lfull[1]), 0u);
         const uint32_t lsend_addr = mapa_u32(smem_u32(lrecv) + (uint32_t)(((int)crank * RG + rg) * 4), 0u);
 
+        const bool loss_lead = want_loss && crank == 0 && tid == 0;
+        unsigned long long* lprev = xprev + 4 * fc;   // [3] loss accumulator values seen complete (cluster 0 only)
+        int l3 = (int)(a.xstep0 % 3);
+        if (loss_lead && q == 0) { lprev[0] = a.lbase[0]; lprev[1] = a.lbase[1]; lprev[2] = a.lbase[2]; }
         uint32_t slot = 0, par = 0;  // this group's ring cursor
         int red_buf = 0;
         long long mb = mb0;
@@ -529,7 +592,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                         for (int rr = 0; rr < RS; ++rr) x[qq * RS + rr] = make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                 }
-                if (tid == 0 && sb == 1) cl_stamp(a, s, 12);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb == 1) cl_stamp(a, s, 12);
                 if (sb == 0 && s > 0) {
                     // the rows of the step's first pass are already in registers: only now wait for the weights
                     take_weights();
@@ -546,7 +609,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                 }
                 MultiReduce<R, 16>::run(d, lane);
                 float z = d[0];  // warp total for row ridx
-                if (tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 8 : 13);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 8 : 13);
                 if (WPG > 1) {
                     float* rb = red + red_buf * (NCW * R);
                     if (canon) rb[(rg * WPG + wig) * R + ridx] = z;
@@ -557,14 +620,14 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                     for (int k = 0; k < WPG; ++k) z += rb[(rg * WPG + k) * R + ridx];
                     red_buf ^= 1;
                 }
-                if (tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 9 : 14);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 9 : 14);
                 float resid = 0.f;
                 if (ridx < rc) {
                     const float yv = ybuf[(size_t)((s & 1) * RG + rg) * a.ycap + sb * R + ridx];
                     resid = sigmoid_f(z) - yv;
                     if (canon && wig == 0 && want_loss) zyb[j * R + ridx] = make_float2(z, yv);
                 }
-                if (tid == 0 && sb == 0) cl_stamp(a, s, 10);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb == 0) cl_stamp(a, s, 10);
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     const float rr = __shfl_sync(0xffffffffu, resid, lane_of_row<R>(r));
@@ -573,7 +636,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                     g.z = fmaf(rr, x[r].z, g.z);
                     g.w = fmaf(rr, x[r].w, g.w);
                 }
-                if (tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 11 : 15);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 11 : 15);
             }
             if (tid == 0) cl_stamp(a, s, 1);
             // ---- hand the gradient chunk to the owner of its columns, straight from registers
@@ -596,8 +659,42 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG>() * 32, 1) lr_clus
                 if (lane == 0)
                     st_async_b32(lsend_addr + (uint32_t)((s & 1) * NSRC * 4), __float_as_uint(l), (s & 1) ? lsend_bar1 : lsend_bar0);
             }
+            // The first compute thread of a cluster's rank-0 CTA sums the cluster's loss partials and adds them to
+            // the step's accumulator; in cluster 0 it also reads the PREVIOUS step's total (complete by now) and
+            // writes it out.  A compute warp has the whole exchange to do this in; an exchange thread has not.
+            // Three accumulators by step: adds of step s+2 need the weights of s+2, i.e. this CTA's gradient of
+            // s+1, which this thread hands off after it has read s-1.
+            if (loss_lead) {
+                const uint32_t lb = smem_u32(&lfull[s & 1]);
+                mbar_wait_cluster(lb, (uint32_t)(s >> 1) & 1u, a.err);
+                float ls = 0.f;
+#pragma unroll
+                for (int k = 0; k < NSRC; ++k) ls += lrecv[(s & 1) * NSRC + k];
+                if (s + 2 < n_steps) mbar_arrive_expect_tx(lb, (uint32_t)NSRC * 4u);
+                red_add_u64(a.lacc + l3, ((unsigned long long)to_fix32(ls) << kClCntBits) + 1ull);
+                if (q == 0 && s > 0) {
+                    const int lp = l3 == 0 ? 2 : l3 - 1;
+                    unsigned long long pv = lprev[lp];
+                    const long long Lt = poll_total<false>(a.lacc + lp, pv, (unsigned)a.ncl, a.err, kErrTimeoutPart, kSpinLimit);
+                    lprev[lp] = pv;
+                    a.loss_out[s - 1] = ((double)Lt * kClFixInv) * a.inv_b;
+                }
+                l3 = l3 == 2 ? 0 : l3 + 1;
+            }
+            __syncwarp();
             if (s + 1 < n_steps) stage_labels(mb_next, (s + 1) & 1);
+            mbar_wait(smem_u32(xdone), (uint32_t)s & 1u, a.err);
             mb = mb_next;
+        }
+        if (loss_lead && q == 0 && n_steps > 0) {  // the last step's loss, and where the accumulators stand
+            const int lp = l3 == 0 ? 2 : l3 - 1;
+            unsigned long long pv = lprev[lp];
+            const long long Lt = poll_total<false>(a.lacc + lp, pv, (unsigned)a.ncl, a.err, kErrTimeoutPart, kSpinLimit);
+            lprev[lp] = pv;
+            a.loss_out[n_steps - 1] = ((double)Lt * kClFixInv) * a.inv_b;
+            a.lbase[0] = lprev[0];
+            a.lbase[1] = lprev[1];
+            a.lbase[2] = lprev[2];
         }
     }
     // nobody leaves while a neighbour may still store into its shared memory

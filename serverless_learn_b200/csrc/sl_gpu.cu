@@ -127,19 +127,28 @@ struct ClVariant {
     int wpg, rg, r, rs, cs, warps;
     const void* fn;
 };
-#define SL_CLUSTER(WPG, RG, R, RS, CS, XW, CREG, XREG) \
-    ClVariant { WPG, RG, R, RS, CS, slk::cl_warps<WPG, RG, XW, CREG>(), \
-                (const void*)slk::lr_cluster_kernel<WPG, RG, R, RS, CS, XW, CREG, XREG> }
+#define SL_CLUSTER_P(WPG, RG, R, RS, CS, XW, CREG, XREG, PW) \
+    ClVariant { WPG, RG, R, RS, CS, slk::cl_warps<WPG, RG, XW, CREG, PW>(), \
+                (const void*)slk::lr_cluster_kernel<WPG, RG, R, RS, CS, XW, CREG, XREG, PW> }
+#define SL_CLUSTER(WPG, RG, R, RS, CS, XW, CREG, XREG) SL_CLUSTER_P(WPG, RG, R, RS, CS, XW, CREG, XREG, 1)
 const ClVariant kClVariants[] = {
     SL_CLUSTER(8, 2, 16, 4, 8, 2, 104, 64),  // 1: F <= 1024, two row groups of 16 rows: a CTA's 32 rows of config 3 in
                                              //    one pass; 20 warps, the compute warpgroups take 104 registers
     SL_CLUSTER(8, 2, 8, 4, 8, 4, 0, 0),      // 2: F <= 1024, two row groups of 8 rows
     SL_CLUSTER(8, 1, 16, 4, 8, 4, 0, 0),     // 3: F <= 1024, one row group (8 compute warps)
     SL_CLUSTER(4, 4, 8, 4, 8, 4, 0, 0),      // 4: F <= 512, four row groups of 8 rows
-    SL_CLUSTER(8, 2, 16, 4, 4, 2, 104, 64),  // 5: as 1 in clusters of 4 (more SMs take part where 8 do not tile the GPCs)
+    SL_CLUSTER(8, 2, 16, 8, 4, 3, 104, 64),  // 5: as 1 in clusters of 4 (more SMs take part where 8 do not tile the GPCs), 8-row slots
     SL_CLUSTER(8, 2, 8, 4, 4, 4, 0, 0),      // 6: as 2 in clusters of 4
     SL_CLUSTER(8, 1, 16, 4, 4, 4, 0, 0),     // 7: as 3 in clusters of 4
-    SL_CLUSTER(8, 2, 16, 4, 2, 2, 104, 64),  // 8: as 1 in clusters of 2
+    SL_CLUSTER(8, 2, 16, 8, 4, 4, 104, 32),  // 8: as 5 with four exchange warps (24 warps, 32 registers for the exchange)
+    SL_CLUSTER(8, 1, 16, 16, 4, 4, 0, 0),    // 9: as 7 with one 16-row ring slot per pass
+    SL_CLUSTER(8, 1, 16, 8, 4, 4, 0, 0),     // 10: as 7 with 8-row ring slots
+    SL_CLUSTER(8, 2, 8, 8, 4, 4, 0, 0),      // 11: as 6 with one 8-row ring slot per pass
+    SL_CLUSTER(8, 1, 16, 16, 8, 4, 0, 0),    // 12: as 3 with one 16-row ring slot per pass
+    SL_CLUSTER(8, 2, 16, 16, 4, 3, 104, 64), // 13: as 5 with one 16-row slot per pass
+    SL_CLUSTER(8, 2, 16, 8, 8, 2, 104, 64),  // 14: as 1 with 8-row slots
+    SL_CLUSTER_P(8, 2, 16, 8, 4, 4, 104, 64, 0),  // 15: as 5 with four exchange warps, one of which also issues the row copies
+    SL_CLUSTER_P(8, 2, 16, 8, 8, 4, 104, 64, 0),  // 16: the same in clusters of 8
 };
 constexpr int kNumClVariants = sizeof(kClVariants) / sizeof(kClVariants[0]);
 
@@ -227,7 +236,7 @@ struct sl_handle {
     int cl_max_clusters[16] = {};        // per variant, for the shared-memory size in cl_smem_set
     size_t cl_smem_set[16] = {};
     int cl_coop = -1;                    // cooperative + cluster launch accepted? (-1 = not tried)
-    long long opt_cl_variant = 0, opt_clusters = 0;
+    long long opt_cl_variant = 0, opt_clusters = 0, opt_poll_delay = -1, opt_poll_gap = -1;
     unsigned long long* mc_gx = nullptr; // multicast alias of the cross-GPU accumulators (sl_peer_attach_multicast)
 
     std::mutex mu;
@@ -689,25 +698,29 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     a.ycap = (a.zy_rows / v.r + v.rg - 1) / v.rg * v.r;  // passes per row group * R
     const size_t yb_b = sizeof(float) * 2 * (size_t)v.rg * a.ycap;
     const size_t slot_b = (size_t)v.rs * a.row_bytes;
-    const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + yb_b + 8 * (2 * 32 + 4) + 512;
+    const size_t prev_b = 8 * (4 * (size_t)a.fc + 4);  // + the loss accumulators' values
+    const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + yb_b + prev_b + 8 * (2 * 32 + 6) + 512;
     if (h->smem_optin < fixed + (size_t)v.rg * slot_b) { *why = "the ring does not fit in shared memory"; return false; }
     size_t nsg = (h->smem_optin - fixed) / ((size_t)v.rg * slot_b);
     nsg = std::min<size_t>(nsg, (size_t)(32 / v.rg));  // one producer lane per slot
     if (h->opt_ring > 0) nsg = std::max<size_t>(1, std::min<size_t>(nsg, (size_t)h->opt_ring));
     a.nsg = (int)nsg;
     size_t off = (size_t)v.rg * nsg * slot_b;
-    off = align_up(off, 16); a.off_bar = (int)off;    off += 8 * (2 * (size_t)v.rg * nsg + 4);
+    off = align_up(off, 16); a.off_bar = (int)off;    off += 8 * (2 * (size_t)v.rg * nsg + 6);
     off = align_up(off, 16); a.off_recv = (int)off;   off += recv_b;
     off = align_up(off, 16); a.off_wsm = (int)off;    off += wsm_b;
     off = align_up(off, 16); a.off_lrecv = (int)off;  off += lrecv_b;
     off = align_up(off, 16); a.off_red = (int)off;    off += red_b;
     off = align_up(off, 16); a.off_zy = (int)off;     off += zy_b;
     off = align_up(off, 16); a.off_yb = (int)off;     off += yb_b;
+    off = align_up(off, 16); a.off_prev = (int)off;   off += prev_b;
     if (off > h->smem_optin) { *why = "shared memory layout exceeds the SM"; return false; }
     const int ranks = fused ? std::max(1, h->peer_n) : 1;
-    a.part_limit = 16777216.0f / (float)((long long)nsrc * ncl * ranks);  // 2^(63-7-32) over all adders
+    a.part_limit = 16777216.0f / (float)((long long)ncl * ranks);  // 2^(63-7-32) over all adders (one per cluster and rank)
     a.eta_over_b = h->eta / ((double)Beff * (double)ranks);
     a.inv_b = 1.0 / (double)Beff;
+    a.poll_delay = h->opt_poll_delay >= 0 ? (int)h->opt_poll_delay : 0;
+    a.poll_gap = h->opt_poll_gap >= 0 ? (int)h->opt_poll_gap : 0;
     p->smem = off;
     p->variant = vi;
     p->grid = grid;
@@ -723,7 +736,7 @@ size_t xblock_bytes_for(int F) { return xblock_gx_offset(F) + 8 * 2 * (size_t)F;
 int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss_dev, bool fused) {
     const ClVariant& v = kClVariants[plan.variant];
     const int F = h->F;
-    const size_t words = 6 * (size_t)F + 8;
+    const size_t words = 6 * (size_t)F + 8;  // gacc, gbase, gxbase [2][F] each; lacc [3] + pad; lbase [3] + pad
     if (!h->cl_scratch || h->cl_scratch_F != F) {
         if (h->cl_scratch) cudaFree(h->cl_scratch);
         h->cl_scratch = nullptr;
@@ -765,7 +778,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         a.gbase = h->cl_scratch + 2 * (size_t)F;
         a.gxbase = h->cl_scratch + 4 * (size_t)F;
         a.lacc = h->cl_scratch + 6 * (size_t)F;
-        a.lbase = a.lacc + 2;
+        a.lbase = a.lacc + 4;
         a.loss_out = loss_dev ? loss_dev + done : nullptr;
         a.xstep0 = h->cl_xstep;
         a.err = h->d_err;
@@ -1215,6 +1228,8 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "sync_path") h->opt_sync_path = value;
     else if (k == "cl_variant") h->opt_cl_variant = value;
     else if (k == "clusters") h->opt_clusters = value;
+    else if (k == "poll_delay") h->opt_poll_delay = value;
+    else if (k == "poll_gap") h->opt_poll_gap = value;
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
 }

@@ -22,6 +22,8 @@ ap.add_argument("--clusters", default="0")
 ap.add_argument("--ring", type=int, default=0)
 ap.add_argument("--loss", type=int, default=1)
 ap.add_argument("--path", type=int, default=6)
+ap.add_argument("--delay", default="-1")
+ap.add_argument("--gap", default="-1")
 ap.add_argument("--timeline", action="store_true")
 a = ap.parse_args()
 peak = 6535.7
@@ -36,6 +38,9 @@ with Replica(a.F, a.B) as r:
     r.set_option("path", a.path)
     for clv in [int(x) for x in a.clv.split(",")]:
         for ncl in [int(x) for x in a.clusters.split(",")]:
+          for delay in [int(x) for x in a.delay.split(",")]:
+           for gap in [int(x) for x in a.gap.split(",")]:
+            r.set_option("poll_delay", delay); r.set_option("poll_gap", gap)
             for steps in [int(x) for x in a.steps.split(",")]:
                 r.set_option("cl_variant", clv); r.set_option("clusters", ncl); r.set_option("ring_slots", a.ring)
                 r.set_option("debug_timeline", -1)
@@ -46,7 +51,7 @@ with Replica(a.F, a.B) as r:
                         r.train_steps(steps, want_loss=bool(a.loss))
                         ts.append(r.last_train_ms())
                     us = float(np.median(ts)) * 1e3 / steps
-                    print(f"clv={clv} grid={r.info('grid')} slots={r.info('ring_slots')} steps={steps} "
+                    print(f"clv={clv} delay={delay} gap={gap} grid={r.info('grid')} slots={r.info('ring_slots')} steps={steps} "
                           f"{us:8.3f} us/step (min {min(ts) * 1e3 / steps:.3f})  {algo / us / 1e3:8.1f} GB/s  "
                           f"frac={algo / us / 1e3 / peak:.3f}", flush=True)
                 except SlError as e:
@@ -71,5 +76,8 @@ with Replica(a.F, a.B) as r:
                     print("  SM-clock deltas (median over CTAs): " + ", ".join(
                         f"{names[b_][:2]}-{names[a_][:2]}={int(np.median(ck[:, b_] - ck[:, a_]))}"
                         for a_, b_ in [(0, 5), (5, 8), (8, 9), (9, 10), (10, 11), (11, 12), (12, 13), (13, 14), (14, 15), (5, 1), (1, 2), (6, 7), (7, 3), (3, 4)]))
+                    for pp in (5, 1, 6):
+                        late = np.argsort(-(t[s, :, pp, 1] - g0))[:6]
+                        print(f"  latest {names[pp][:2]} CTAs:", late.tolist(), (t[s, late, pp, 1] - g0).tolist())
                     nxt = t[s + 1, :, 0, 1] - g0
                     print(f"  next step start        {nxt.min():7d} {int(np.median(nxt)):7d} {nxt.max():7d}")
