@@ -23,7 +23,8 @@ TARGETS = {
     "libsl_gpu.so": dict(
         srcs=["sl_gpu.cu"], deps=["kernels.cuh", "kernels_wide.cuh", "kernels_multi.cuh", "kernels_cluster.cuh", "../../include/sl_gpu.h"],
         cmd=lambda out, srcs: [NVCC, *ARCH, "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
-                               "-shared", "-cudart", "static", "-o", out, *srcs, "-ldl"]),
+                               "-shared", "-cudart", "static", *os.environ.get("SL_NVCC_DEFS", "").split(),
+                               "-o", out, *srcs, "-ldl"]),
     "libsl_roles.so": dict(
         srcs=["roles.cc"], deps=["roles.h", "wire.h", "../../include/sl_roles.h",
                                  "../../include/sl_gpu.h"],

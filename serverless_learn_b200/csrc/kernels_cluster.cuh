@@ -35,7 +35,13 @@ namespace slk {
 constexpr int kClCntBits = 7;                                  // arrivals per word: up to 127 adders
 constexpr unsigned long long kClCntMask = (1ull << kClCntBits) - 1ull;
 constexpr double kClFixInv = 1.0 / 4294967296.0;               // fixed point: 2^-32 units
-constexpr int kErrRange = 5;                                   // a gradient partial left the fixed-point range
+constexpr int kErrRange = 5;
+// Accumulator replicas: cluster q adds into replica q % kClRep, readers sum the replicas — fewer adders per
+// L2 word (the atomic unit serialises them), more words to poll.
+#ifndef SL_CL_KREP
+#define SL_CL_KREP 1
+#endif
+constexpr int kClRep = SL_CL_KREP;                                   // a gradient partial left the fixed-point range
 
 struct ClArgs {
     const float* X;        // [n_rows, F] row-major, resident shard
@@ -227,6 +233,37 @@ __device__ __forceinline__ void poll_totals(unsigned long long* const (&p)[XC], 
     }
 }
 
+template <bool SYS, int XI>
+__device__ __forceinline__ void poll_totals_w(unsigned long long* const (&p)[XI], const bool (&act)[XI],
+                                              unsigned long long (&prev)[XI], long long (&T)[XI],
+                                              const unsigned (&want)[XI], int* err, int code, uint32_t limit) {
+    bool done[XI];
+#pragma unroll
+    for (int i = 0; i < XI; ++i) done[i] = !act[i] || want[i] == 0;
+    uint32_t spins = 0;
+    for (;;) {
+        unsigned long long v[XI];
+#pragma unroll
+        for (int i = 0; i < XI; ++i)
+            if (!done[i]) v[i] = SYS ? ld_relaxed_sys_u64(p[i]) : ld_relaxed_u64(p[i]);
+        bool all = true;
+#pragma unroll
+        for (int i = 0; i < XI; ++i) {
+            if (done[i]) continue;
+            const unsigned long long d = v[i] - prev[i];
+            if ((d & kClCntMask) == (unsigned long long)want[i]) {
+                done[i] = true;
+                prev[i] = v[i];
+                T[i] = (long long)(d - (unsigned long long)want[i]) >> kClCntBits;
+            } else {
+                all = false;
+            }
+        }
+        if (all) break;
+        if (spin_abort(spins, err, code, limit)) break;
+    }
+}
+
 // WPG warps cover a row (one float4 column chunk per thread: F <= 128*WPG); RG row groups of WPG warps
 // take R rows each per pass, from their own ring of RS-row slots; CS = CTAs per cluster; XW exchange
 // warps share the (at most 128) columns this CTA owns.  CREG > 0: the compute warpgroups take CREG
@@ -284,6 +321,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     const uint32_t recv_bytes = (uint32_t)NSRC * (uint32_t)fc * 4u;
 
     if (tid == 0) {
+        if (!SL_CL_FINE_STAMPS) cl_stamp(a, a.dbg_step, 14);  // kernel entry
         for (int s = 0; s < RG * nsg; ++s) {
             mbar_init(smem_u32(&full[s]), 1);
             mbar_init(smem_u32(&empty[s]), WPG);
@@ -370,6 +408,10 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     } else if (warp >= NCW) {
         // ======================================================================= exchange
         if (CREG > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(XREG > 0 ? XREG : 24));
+        if (!PW && warp == NCW) {  // first use of every ring slot, before anything that waits for global memory
+            produce(-1);
+            __syncwarp();
+        }
         const int t = (warp - NCW) * 32 + lane;
         bool xact[XC];
         int col[XC];
@@ -384,23 +426,24 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             col[i] = (int)crank * fc + tl;
             master[i] = xact[i] ? a.model[col[i]] : 0.0;
             if (xact[i]) {
-                xprev[0 * fc + tl] = a.gbase[col[i]];
-                xprev[1 * fc + tl] = a.gbase[F + col[i]];
+                for (int k = 0; k < 2 * kClRep; ++k) xprev[k * fc + tl] = a.gbase[(size_t)k * F + col[i]];
                 if (a.nranks > 1) {
-                    xprev[2 * fc + tl] = a.gxbase[col[i]];
-                    xprev[3 * fc + tl] = a.gxbase[F + col[i]];
+                    xprev[(2 * kClRep) * fc + tl] = a.gxbase[col[i]];
+                    xprev[(2 * kClRep + 1) * fc + tl] = a.gxbase[F + col[i]];
                 }
             }
             xsend[i] = a.nranks > 1 && xact[i] && (tl % a.ncl) == q;
         }
         const uint32_t wfull_a = smem_u32(wfull), wsm_a = smem_u32(wsm);
-        if (!PW && warp == NCW) {  // first use of every ring slot
-            produce(-1);
-            __syncwarp();
-        }
 
         for (int s = 0; s < n_steps; ++s) {
             const int b = (int)((a.xstep0 + s) & 1);
+            if (!PW && warp == NCW && s == 0) {
+                // cold start: the slots of step 0 are free again as soon as its rows have gone into registers —
+                // refill them now, not after this step's exchange (later steps refill after the weights went out)
+                produce(0);
+                __syncwarp();
+            }
             mbar_wait_cluster(smem_u32(rfull), (uint32_t)s & 1u, a.err);
             if (t == 0) {
                 cl_stamp(a, s, 6);
@@ -427,13 +470,22 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 bad = bad || !(fabsf(v[0]) < a.part_limit);
                 P[i] = to_fix32(v[0]);
             }
-            unsigned long long* gp[XC];
-            unsigned long long pv[XC];
+            // local accumulators: [2 buffers][kClRep replicas][F]; this cluster adds into replica q % kClRep
+            constexpr int XI = XC * kClRep;
+            unsigned long long* lp[XI];
+            unsigned long long lpv[XI];
+            bool lact[XI];
+            long long LT[XI];
 #pragma unroll
             for (int i = 0; i < XC; ++i) {
-                gp[i] = a.gacc + (size_t)b * F + col[i];
-                pv[i] = xact[i] ? xprev[b * fc + t + i * XT] : 0ull;
-                if (xact[i]) red_add_u64(gp[i], ((unsigned long long)P[i] << kClCntBits) + 1ull);
+#pragma unroll
+                for (int k = 0; k < kClRep; ++k) {
+                    lp[i * kClRep + k] = a.gacc + ((size_t)(b * kClRep + k)) * F + col[i];
+                    lact[i * kClRep + k] = xact[i];
+                    lpv[i * kClRep + k] = xact[i] ? xprev[((b * kClRep + k) * fc) + t + i * XT] : 0ull;
+                    LT[i * kClRep + k] = 0;
+                }
+                if (xact[i]) red_add_u64(lp[i * kClRep + (kClRep > 1 ? q % kClRep : 0)], ((unsigned long long)P[i] << kClCntBits) + 1ull);
             }
             // the compute warps hold back their next burst of shared-memory loads (pulling the next step's rows
             // into registers) until the partials have been read: the two would queue in the same pipe
@@ -441,17 +493,32 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             if (lane == 0) mbar_arrive(smem_u32(xdone));
             if (bad) atomicCAS(a.err, 0, kErrRange);
             if (t == 0) cl_stamp(a, s, 7);
-            poll_totals<false, XC>(gp, xact, pv, T, (unsigned)a.ncl, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPart, kSpinLimit);
+            if (kClRep == 1) {
+                poll_totals<false, XI>(lp, lact, lpv, LT, (unsigned)a.ncl, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPart, kSpinLimit);
+            } else {
+                // replica k is complete when the clusters q with q % kClRep == k have added
+                unsigned wantk[XI];
 #pragma unroll
-            for (int i = 0; i < XC; ++i)
-                if (xact[i]) xprev[b * fc + t + i * XT] = pv[i];
+                for (int i = 0; i < XI; ++i) wantk[i] = (unsigned)((a.ncl - (i % kClRep) + kClRep - 1) / kClRep);
+                poll_totals_w<false, XI>(lp, lact, lpv, LT, wantk, a.err, kErrTimeoutPart, kSpinLimit);
+            }
+#pragma unroll
+            for (int i = 0; i < XC; ++i) {
+#pragma unroll
+                for (int k = 0; k < kClRep; ++k) {
+                    if (xact[i]) xprev[((b * kClRep + k) * fc) + t + i * XT] = lpv[i * kClRep + k];
+                    T[i] += LT[i * kClRep + k];
+                }
+            }
+            unsigned long long* gp[XC];
+            unsigned long long pv[XC];
             if (t == 0) cl_stamp(a, s, 3);
             if (a.nranks > 1) {
                 // this GPU's total of a column goes to every rank's accumulator; then wait for all ranks'
 #pragma unroll
                 for (int i = 0; i < XC; ++i) {
                     gp[i] = a.peer_gx[a.rank] + (size_t)b * F + col[i];
-                    pv[i] = xact[i] ? xprev[(2 + b) * fc + t + i * XT] : 0ull;
+                    pv[i] = xact[i] ? xprev[(2 * kClRep + b) * fc + t + i * XT] : 0ull;
                     if (!xsend[i]) continue;
                     const unsigned long long val = ((unsigned long long)T[i] << kClCntBits) + 1ull;
                     const size_t off = (size_t)b * F + col[i];
@@ -464,7 +531,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 poll_totals<true, XC>(gp, xact, pv, T, (unsigned)a.nranks, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPeer, kPeerSpinLimit);
 #pragma unroll
                 for (int i = 0; i < XC; ++i)
-                    if (xact[i]) xprev[(2 + b) * fc + t + i * XT] = pv[i];
+                    if (xact[i]) xprev[(2 * kClRep + b) * fc + t + i * XT] = pv[i];
             }
             // new fp32 weights to every CTA of the cluster, 16 bytes per store: the four lanes of a quad hold
             // four consecutive columns; each gathers the quad's values and serves a quarter of the CTAs
@@ -501,11 +568,10 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 if (!xact[i]) continue;
                 a.model[col[i]] = master[i];
                 const int tl = t + i * XT;
-                a.gbase[col[i]] = xprev[0 * fc + tl];
-                a.gbase[F + col[i]] = xprev[1 * fc + tl];
+                for (int k = 0; k < 2 * kClRep; ++k) a.gbase[(size_t)k * F + col[i]] = xprev[k * fc + tl];
                 if (a.nranks > 1) {
-                    a.gxbase[col[i]] = xprev[2 * fc + tl];
-                    a.gxbase[F + col[i]] = xprev[3 * fc + tl];
+                    a.gxbase[col[i]] = xprev[(2 * kClRep) * fc + tl];
+                    a.gxbase[F + col[i]] = xprev[(2 * kClRep + 1) * fc + tl];
                 }
             }
         }
@@ -535,7 +601,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
         const uint32_t lsend_addr = mapa_u32(smem_u32(lrecv) + (uint32_t)(((int)crank * RG + rg) * 4), 0u);
 
         const bool loss_lead = want_loss && crank == 0 && tid == 0;
-        unsigned long long* lprev = xprev + 4 * fc;   // [3] loss accumulator values seen complete (cluster 0 only)
+        unsigned long long* lprev = xprev + (2 * kClRep + 2) * fc;   // [3] loss accumulator values seen complete (cluster 0 only)
         int l3 = (int)(a.xstep0 % 3);
         if (loss_lead && q == 0) { lprev[0] = a.lbase[0]; lprev[1] = a.lbase[1]; lprev[2] = a.lbase[2]; }
         uint32_t slot = 0, par = 0;  // this group's ring cursor
@@ -558,7 +624,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
 
         for (int s = 0; s < n_steps; ++s) {
             const long long mb_next = wrap(mb + a.vB);
-            float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+            float2 glo = make_float2(0.f, 0.f), ghi = make_float2(0.f, 0.f);  // gradient of this thread's four columns
             float2* zyb = zy + (size_t)(s & 1) * a.zy_rows;
             if (tid == 0) cl_stamp(a, s, 0);
             auto take_weights = [&]() {
@@ -598,14 +664,14 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                     take_weights();
                     if (tid == 0) cl_stamp(a, s, 5);
                 }
+                // packed fp32 pairs (FFMA2): half the issue slots of the two inner loops
                 float d[R];
+                const float2 wlo = make_float2(w.x, w.y), whi = make_float2(w.z, w.w);
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    float acc = x[r].x * w.x;
-                    acc = fmaf(x[r].y, w.y, acc);
-                    acc = fmaf(x[r].z, w.z, acc);
-                    acc = fmaf(x[r].w, w.w, acc);
-                    d[r] = acc;
+                    float2 acc = __ffma2_rn(make_float2(x[r].x, x[r].y), wlo, make_float2(0.f, 0.f));
+                    acc = __ffma2_rn(make_float2(x[r].z, x[r].w), whi, acc);
+                    d[r] = acc.x + acc.y;
                 }
                 MultiReduce<R, 16>::run(d, lane);
                 float z = d[0];  // warp total for row ridx
@@ -624,23 +690,22 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 float resid = 0.f;
                 if (ridx < rc) {
                     const float yv = ybuf[(size_t)((s & 1) * RG + rg) * a.ycap + sb * R + ridx];
-                    resid = sigmoid_f(z) - yv;
+                    resid = __frcp_rn(1.0f + __expf(-z)) - yv;  // MUFU.EX2 / MUFU.RCP: ~2 ulp, far inside the tolerance
                     if (canon && wig == 0 && want_loss) zyb[j * R + ridx] = make_float2(z, yv);
                 }
                 if (SL_CL_FINE_STAMPS && tid == 0 && sb == 0) cl_stamp(a, s, 10);
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     const float rr = __shfl_sync(0xffffffffu, resid, lane_of_row<R>(r));
-                    g.x = fmaf(rr, x[r].x, g.x);
-                    g.y = fmaf(rr, x[r].y, g.y);
-                    g.z = fmaf(rr, x[r].z, g.z);
-                    g.w = fmaf(rr, x[r].w, g.w);
+                    const float2 rr2 = make_float2(rr, rr);
+                    glo = __ffma2_rn(rr2, make_float2(x[r].x, x[r].y), glo);
+                    ghi = __ffma2_rn(rr2, make_float2(x[r].z, x[r].w), ghi);
                 }
                 if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 11 : 15);
             }
             if (tid == 0) cl_stamp(a, s, 1);
             // ---- hand the gradient chunk to the owner of its columns, straight from registers
-            if (gv) st_async_v4(send_addr, g, send_bar);
+            if (gv) st_async_v4(send_addr, make_float4(glo.x, glo.y, ghi.x, ghi.y), send_bar);
             if (tid == 0) cl_stamp(a, s, 2);
             // ---- off the critical path: this group's loss of the step
             if (wig == 0 && want_loss) {
@@ -700,6 +765,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     // nobody leaves while a neighbour may still store into its shared memory
     __syncwarp();
     cluster_sync_all();
+    if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp(a, a.dbg_step, 15);  // kernel exit
 }
 
 }  // namespace slk

@@ -666,9 +666,24 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
         vi = (int)h->opt_cl_variant - 1;
         if (!fits(kClVariants[vi])) { *why = "requested cluster variant does not hold this F"; return false; }
     } else {
-        const int order[] = {F <= 512 ? 4 : 1, 1};
-        for (int k : order)
-            if (fits(kClVariants[k - 1])) { vi = k - 1; break; }
+        // measured at config 3 (tools/k1c_bench.py, profiles/r2_k1c.md): clusters of 4 put 132 of the 148 SMs to
+        // work (clusters of 8 only tile 120); with at most 32 rows per CTA and step the whole step is one pass of
+        // two 16-row groups and the row copies are issued by an exchange warp (15), otherwise by their own warp (5)
+        if (F <= 512) {
+            vi = 3;
+        } else {
+            const long long beff = (long long)h->B * (h->vw > 1 ? h->vw : 1);
+            int ncl5 = cluster_capacity(h, 4);
+            if (h->opt_clusters > 0) ncl5 = (int)std::min<long long>(ncl5, h->opt_clusters);
+            else if (h->opt_grid > 0) ncl5 = (int)std::max<long long>(1, std::min<long long>(ncl5, h->opt_grid / 4));
+            const long long rows_cta = ncl5 > 0 ? (beff + 4LL * ncl5 - 1) / (4LL * ncl5) : 1 << 30;
+            vi = rows_cta <= 32 ? 14 : 4;
+        }
+        if (!fits(kClVariants[vi]) || cluster_capacity(h, vi) < 1) {
+            vi = -1;
+            for (int k = 0; k < kNumClVariants; ++k)
+                if (fits(kClVariants[k]) && cluster_capacity(h, k) >= 1) { vi = k; break; }
+        }
         if (vi < 0) { *why = "F must be a multiple of 32 and at most 1024 for the cluster kernel"; return false; }
     }
     const ClVariant& v = kClVariants[vi];
@@ -698,7 +713,7 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     a.ycap = (a.zy_rows / v.r + v.rg - 1) / v.rg * v.r;  // passes per row group * R
     const size_t yb_b = sizeof(float) * 2 * (size_t)v.rg * a.ycap;
     const size_t slot_b = (size_t)v.rs * a.row_bytes;
-    const size_t prev_b = 8 * (4 * (size_t)a.fc + 4);  // + the loss accumulators' values
+    const size_t prev_b = 8 * ((2 * slk::kClRep + 2) * (size_t)a.fc + 4);  // + the loss accumulators' values
     const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + yb_b + prev_b + 8 * (2 * 32 + 6) + 512;
     if (h->smem_optin < fixed + (size_t)v.rg * slot_b) { *why = "the ring does not fit in shared memory"; return false; }
     size_t nsg = (h->smem_optin - fixed) / ((size_t)v.rg * slot_b);
@@ -736,7 +751,8 @@ size_t xblock_bytes_for(int F) { return xblock_gx_offset(F) + 8 * 2 * (size_t)F;
 int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss_dev, bool fused) {
     const ClVariant& v = kClVariants[plan.variant];
     const int F = h->F;
-    const size_t words = 6 * (size_t)F + 8;  // gacc, gbase, gxbase [2][F] each; lacc [3] + pad; lbase [3] + pad
+    const size_t KR = slk::kClRep;
+    const size_t words = (4 * KR + 2) * (size_t)F + 8;  // gacc, gbase [2][KR][F]; gxbase [2][F]; lacc [3] + pad; lbase [3] + pad
     if (!h->cl_scratch || h->cl_scratch_F != F) {
         if (h->cl_scratch) cudaFree(h->cl_scratch);
         h->cl_scratch = nullptr;
@@ -775,9 +791,9 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         a.n_steps = n;
         a.model = h->model;
         a.gacc = h->cl_scratch;
-        a.gbase = h->cl_scratch + 2 * (size_t)F;
-        a.gxbase = h->cl_scratch + 4 * (size_t)F;
-        a.lacc = h->cl_scratch + 6 * (size_t)F;
+        a.gbase = h->cl_scratch + 2 * KR * (size_t)F;
+        a.gxbase = h->cl_scratch + 4 * KR * (size_t)F;
+        a.lacc = h->cl_scratch + (4 * KR + 2) * (size_t)F;
         a.lbase = a.lacc + 4;
         a.loss_out = loss_dev ? loss_dev + done : nullptr;
         a.xstep0 = h->cl_xstep;
@@ -1230,6 +1246,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "clusters") h->opt_clusters = value;
     else if (k == "poll_delay") h->opt_poll_delay = value;
     else if (k == "poll_gap") h->opt_poll_gap = value;
+    else if (k == "cl_coop") h->cl_coop = value < 0 ? -1 : (value ? 1 : 0);
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
 }

@@ -23,8 +23,10 @@ ap.add_argument("--ring", type=int, default=0)
 ap.add_argument("--loss", type=int, default=1)
 ap.add_argument("--path", type=int, default=6)
 ap.add_argument("--delay", default="-1")
+ap.add_argument("--coop", type=int, default=-1)
 ap.add_argument("--gap", default="-1")
 ap.add_argument("--timeline", action="store_true")
+ap.add_argument("--span", type=int, default=0, help="steps of one call whose entry/exit stamps are compared with the event time")
 a = ap.parse_args()
 peak = 6535.7
 algo = 4 * (a.F + 1) * a.B + 16 * a.F
@@ -36,6 +38,7 @@ order = [0, 5, 8, 9, 10, 11, 12, 13, 14, 15, 1, 2, 6, 7, 3, 4]
 with Replica(a.F, a.B) as r:
     r.shard_synth(a.rows)
     r.set_option("path", a.path)
+    r.set_option("cl_coop", a.coop)
     for clv in [int(x) for x in a.clv.split(",")]:
         for ncl in [int(x) for x in a.clusters.split(",")]:
           for delay in [int(x) for x in a.delay.split(",")]:
@@ -57,6 +60,21 @@ with Replica(a.F, a.B) as r:
                 except SlError as e:
                     print(f"clv={clv} clusters={ncl}: {e}", flush=True)
                     continue
+            if a.span:
+                r.set_option("debug_timeline", 0)
+                r.train_steps(a.span, want_loss=bool(a.loss))
+                ms = r.last_train_ms()
+                G = r.info("grid")
+                buf = np.zeros(4 * G * 32, dtype=np.uint64)
+                assert r._L.sl_debug_read(r._h, buf.ctypes.data_as(C.POINTER(C.c_ulonglong)), buf.size) == 0
+                t = buf.reshape(4, G, 16, 2).astype(np.int64)
+                ent, ext = t[0, :, 14, 1], t[0, :, 15, 1]
+                e0 = ent.min()
+                print(f"span of a {a.span}-step call: event time {ms * 1e3:.2f} us; kernel entry spread {ent.max() - e0} ns, "
+                      f"exit {ext.min() - e0}..{ext.max() - e0} ns after the first entry")
+                for s_ in range(min(4, a.span)):
+                    print(f"  step {s_}: P0 {np.median(t[s_, :, 0, 1]) - e0:.0f}  P5 {np.median(t[s_, :, 5, 1]) - e0:.0f}  P1 {np.median(t[s_, :, 1, 1]) - e0:.0f}  "
+                          f"P7 {np.median(t[s_, :, 7, 1]) - e0:.0f}  P3 {np.median(t[s_, :, 3, 1]) - e0:.0f}  P4 {np.median(t[s_, :, 4, 1]) - e0:.0f} (median ns after the first entry)")
             if a.timeline:
                 r.set_option("debug_timeline", 10)
                 r.train_steps(32, want_loss=bool(a.loss))
