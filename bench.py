@@ -17,6 +17,12 @@ Prints ONE JSON line (rank 0).  Keys beyond the base contract:
   e2e           the same metric through the C ABI with HOST buffers: per step one
                 minibatch is streamed from pinned host memory (sl_shard_*), one step is
                 taken and its loss is read back
+  repeats       the timed K-step call is repeated (barrier + synchronize around each) and
+                the MEDIAN device time is reported; ms_per_step_all lists them all
+  exchange_us   the update-exchange calls (merge / delta / apply / one-kernel gossip round)
+                as blocking C-ABI calls, microseconds per call at D = 1024 and 16384
+  N > 1         ranks_bit_identical (a hash of every rank's fp64 model after the warm-up)
+                and sync_parity_err (first steps against the oracle's W-worker loop)
 """
 from __future__ import annotations
 
@@ -60,12 +66,14 @@ def measured_peak():
 
 
 def ncu_traffic_per_step():
+    """DRAM bytes per step from the committed ncu capture (a citation of that run, not a measurement of this one)."""
     p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     try:
         with open(p) as fh:
-            return float(json.load(fh)["dram_bytes_per_step"])
+            d = json.load(fh)
+        return float(d["dram_bytes_per_step"]), "profiles/ncu_traffic.json: " + d.get("source", "ncu capture, N=1")
     except Exception:
-        return None
+        return None, None
 
 
 class ClockSampler(threading.Thread):
@@ -219,26 +227,61 @@ def run_b200(args, rank, world, local_rank):
         attach_peers(r)
     step_fn = r.train_steps_sync if multi else r.train_steps
 
+    # ---- N > 1: parity where the driver can see it (outside any timed region) ---------------
+    sync_parity_err = None
+    if multi:
+        import oracle  # checker only
+        psteps = 3
+        lg = step_fn(psteps, want_loss=True)
+        wg = torch.from_numpy(r.model()).cuda()
+        allw = [torch.zeros(F, dtype=torch.float64, device="cuda") for _ in range(world)]
+        dist.all_gather(allw, wg)
+        if rank == 0:
+            orc = oracle.Oracle()
+            sh = [orc.synth(shard_row0(k), psteps * B, F) for k in range(world)]
+            wref = np.zeros(F)
+            lo = orc.lr_steps_sync([x[0] for x in sh], [x[1] for x in sh], B, 0, psteps, wref, ETA,
+                                   threads=min(world, orc.max_threads()))
+            ew = float(np.max(np.abs(allw[0].cpu().numpy() - wref)) / np.max(np.abs(wref)))
+            el = float(np.max(np.abs(lg - lo) / lo))
+            sync_parity_err = {"weights": ew, "loss": el, "steps": psteps,
+                               "against": "oracle lr_steps_sync over the ranks' first minibatches"}
+        r.set_state(np.zeros(F), np.zeros(F))
+        r.set_option("step", 0)
+
     # ---- device-resident leg ("value") ------------------------------------------------
     step_fn(args.warmup, want_loss=True)
+    ranks_bit_identical = None
+    if multi:   # every rank must hold the same fp64 model, bit for bit
+        mine = torch.from_numpy(r.model().view(np.int64).copy()).cuda()
+        allm = [torch.zeros(F, dtype=torch.int64, device="cuda") for _ in range(world)]
+        dist.all_gather(allm, mine)
+        ranks_bit_identical = all(bool(torch.equal(allm[0], x)) for x in allm)
     sampler = ClockSampler(local_rank)
     barrier()
     l0 = r.info("launches")
     k0 = r.info("k1_launches")
     sampler.start()
-    t0 = time.perf_counter()
-    step_fn(args.steps, want_loss=True)      # every step's loss is computed and read back
-    torch.cuda.synchronize()
-    wall = time.perf_counter() - t0
+    dev_all, wall_all = [], []
+    for _ in range(args.repeats):            # EXACTLY K steps per repeat, barrier + synchronize around each
+        barrier()
+        t0 = time.perf_counter()
+        step_fn(args.steps, want_loss=True)      # every step's loss is computed and read back
+        torch.cuda.synchronize()
+        wall_all.append(max_over_ranks(time.perf_counter() - t0))
+        dev_all.append(max_over_ranks(r.last_train_ms() * 1e-3))
     sampler.stop_flag = True
-    dev_ms = r.last_train_ms()
-    launches = r.info("launches") - l0
-    k1 = max(1, r.info("k1_launches") - k0) if r.info("path") in (1, 4) else max(1, launches)
+    launches = (r.info("launches") - l0) // args.repeats
+    path_used, variant_used, grid_used, slots_used = r.info("path"), r.info("variant"), r.info("grid"), r.info("ring_slots")
+    k1 = max(1, (r.info("k1_launches") - k0) // args.repeats) if path_used in (1, 4, 6, 7) else max(1, launches)
     barrier()
     sampler.join(timeout=1.0)
-    dev_s = max_over_ranks(dev_ms * 1e-3)
-    wall_s = max_over_ranks(wall)
+    dev_s = float(np.median(dev_all))
+    wall_s = float(np.median(wall_all))
+    dev_ms = dev_s * 1e3
     value = world * args.steps * B / dev_s
+    r.close()                                 # its 4 GiB shard is not needed below
+    barrier()
 
     # ---- end-to-end leg: host buffers through the C ABI ---------------------------------
     pool = 8
@@ -251,7 +294,7 @@ def run_b200(args, rank, world, local_rank):
         raw = gen.shard_read(0, gen.shard_bytes())
         hb.copy_(torch.from_numpy(raw.view(np.float32)))
     gen.close()
-    e2e_steps = int(min(args.steps, 512))
+    e2e_steps = 256                           # long enough for the copy/compute pipeline to settle, whatever --steps is
     nbytes = B * (F + 1) * 4
     e2e = Replica(F, B, eta=ETA, device=local_rank)
     if multi:
@@ -272,7 +315,7 @@ def run_b200(args, rank, world, local_rank):
     # trained on and its loss is read back; sl_shard_end waits for the copy and swaps it in
     ingest(0)
     e2e.shard_end()
-    for i in range(max(3, min(args.warmup, 16))):
+    for i in range(16):
         ingest(i + 1)
         e2e_step(1, want_loss=True)
         e2e.shard_end()
@@ -314,7 +357,7 @@ def run_b200(args, rank, world, local_rank):
     # not the headline workload: one more line of evidence for the wide-row kernel (K1w)
     wide = None
     try:
-        WF, WB, wrows, wsteps = 16384, 16384, 1 << 17, 64
+        WF, WB, wrows, wsteps = 16384, 16384, 1 << 20, 64      # 2^20 rows x 16384 fp32 = 64 GiB resident per GPU
         rw = Replica(WF, WB, eta=ETA, device=local_rank)
         rw.shard_synth(wrows, row0=rank * wrows)
         if multi:
@@ -331,7 +374,8 @@ def run_b200(args, rank, world, local_rank):
         torch.cuda.synchronize()
         w_s = max_over_ranks(rw.last_train_ms() * 1e-3)
         barrier()
-        wide = {"workload": f"config 5 shape: F={WF}, B={WB} per GPU, {wrows} rows resident per GPU (8 GiB > L2)",
+        wide = {"workload": f"config 5: F={WF}, B={WB} per GPU, {wrows} rows resident per GPU (64 GiB), "
+                            f"{world * wrows} rows over {world} GPU(s)",
                 "value": world * wsteps * WB / w_s, "unit": UNIT, "ms_per_step": 1e3 * w_s / wsteps,
                 "steps": wsteps, "variant": rw.info("variant"),
                 "hbm_gbs_per_gpu": algorithmic_bytes_per_step(WF, WB) * wsteps / w_s / 1e9}
@@ -385,6 +429,33 @@ def run_b200(args, rank, world, local_rank):
         except Exception as ex:  # the headline line must not depend on this extra
             c2 = {"error": repr(ex)}
 
+    # ---- extra: the update-exchange calls as blocking C-ABI calls, us per call ----
+    xus = None
+    if rank == 0:
+        try:
+            xus = {}
+            for D in (1024, 16384):
+                with Replica(D, 64, device=local_rank) as xa, Replica(D, 64, device=local_rank) as xb:
+                    dvec = np.random.default_rng(0).normal(size=D)
+                    xa.set_state(dvec, np.zeros(D))
+                    xb.set_state(-dvec, np.zeros(D))
+
+                    def per_call(fn, n=300):
+                        for _ in range(30):
+                            fn()
+                        t0 = time.perf_counter()
+                        for _ in range(n):
+                            fn()
+                        return (time.perf_counter() - t0) / n * 1e6
+
+                    xus[f"D={D}"] = {"merge": per_call(lambda: xa.exchange_updates(dvec)),
+                                     "delta": per_call(lambda: xa.delta()),
+                                     "apply": per_call(lambda: xa.apply_reply(dvec)),
+                                     "gossip_p2p": per_call(lambda: xa.gossip_p2p(xb))}
+            xus["what"] = "host wall time per blocking call, host buffers in and out"
+        except Exception as ex:
+            xus = {"error": repr(ex)}
+
     if rank == 0:
         peak, peak_src = measured_peak()
         if c2 and "hbm_gbs" in c2:
@@ -394,7 +465,7 @@ def run_b200(args, rank, world, local_rank):
         algo = algorithmic_bytes_per_step() * args.steps / k1
         per_launch_s = dev_ms * 1e-3 / k1
         achieved = algo / per_launch_s / 1e9
-        traffic = ncu_traffic_per_step()
+        traffic, traffic_src = ncu_traffic_per_step()
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
@@ -407,31 +478,41 @@ def run_b200(args, rank, world, local_rank):
                        "parallelism": f"dp{world}" + (" (gradient summed across GPUs every step inside the persistent "
                                                       "kernel, through peer memory over NVLink)" if multi else ""),
                        "kernel_path": {1: "persistent", 2: "simple", 3: "simple+nccl",
-                                       4: "persistent+peer-memory exchange"}.get(r.info("path"), "?"),
-                       "variant": r.info("variant"), "grid": r.info("grid"),
-                       "ring_slots": r.info("ring_slots")},
+                                       4: "persistent+peer-memory exchange", 6: "cluster",
+                                       7: "cluster+peer-memory exchange"}.get(path_used, "?"),
+                       "variant": variant_used, "grid": grid_used, "ring_slots": slots_used},
             "wall_ms_per_step": 1e3 * wall_s / args.steps,
+            "repeats": args.repeats, "ms_per_step_all": [1e3 * x / args.steps for x in dev_all],
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None if traffic is None else traffic * args.steps / k1,
+                         "frac": achieved / peak,
+                         "traffic": None if (traffic is None or multi) else traffic * args.steps / k1,
+                         "traffic_source": None if (traffic is None or multi) else traffic_src,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_step": algorithmic_bytes_per_step(),
-                         "kernel": "lr_persist_kernel" if r.info("path") in (1, 4) else "lr_fwd+lr_grad+lr_finish",
+                         "kernel": {1: "lr_persist_kernel", 4: "lr_persist_kernel", 6: "lr_cluster_kernel",
+                                    7: "lr_cluster_kernel"}.get(path_used, "lr_fwd+lr_grad+lr_finish"),
                          "launches": k1},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes,
-                    "d2h_bytes_per_step": 8, "steps": e2e_steps, "last_loss": float(loss)},
+                    "d2h_bytes_per_step": 8, "steps": e2e_steps, "last_loss": float(loss),
+                    "pcie_gbs": world * e2e_steps * nbytes / e2e_s / 1e9 / world,
+                    "note": "every sample crosses PCIe once and is used once: 4,100 B per sample bounds this leg at "
+                            "host-to-device bandwidth / 4100, whatever the kernel does"},
             "e2e_resident": {"value": world * res_steps * B / res_s, "unit": UNIT,
                              "what": f"ingest {res_rows} rows ({res_bytes} B) from pinned host memory through "
                                      f"sl_shard_*, then {epochs} epochs = {res_steps} steps with every loss read "
                                      "back, all timed", "h2d_bytes": res_bytes, "d2h_bytes": 8 * res_steps},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(launches),   # kernels of one timed K-step call
             "clocks": sampler.result(),
-            "config5_shape": wide,
+            "config5": wide,
             "config2": c2,
+            "exchange_us": xus,
         }
+        if multi:
+            line["ranks_bit_identical"] = ranks_bit_identical
+            line["sync_parity_err"] = sync_parity_err
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_port()
         emit(line)
-    r.close()
     e2e.close()
     if multi:
         dist.destroy_process_group()
@@ -455,11 +536,13 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=16384)
-    ap.add_argument("--warmup", type=int, default=256)
+    ap.add_argument("--steps", type=int, default=2048)
+    ap.add_argument("--warmup", type=int, default=64)
+    ap.add_argument("--repeats", type=int, default=9)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    args.repeats = max(args.repeats, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -88,8 +88,9 @@ int sl_debug_read(sl_handle* h, unsigned long long* out, size_t n_words);
  * sl_shard_checksum quantities, over the bytes after the header) must match — and the payload
  * after the header is what gets trained on.  A mismatch fails sl_shard_end (SL_EINVAL) and keeps
  * the previously sealed shard.  Streams without the magic are taken verbatim as before.
- * A stream that does not hold one complete row seals nothing: sl_shard_end returns SL_OK with
- * *n_rows = 0 and the previously sealed shard (if any) stays the one that is trained on. */
+ * A stream that does not hold one complete row never replaces a trainable shard: sl_shard_end
+ * returns SL_OK with *n_rows = 0 and the previously sealed shard stays the one that is trained on
+ * (on a handle that holds no rows yet, the bytes are kept as an untrainable shard of zero rows). */
 #define SL_SHARD_MAGIC "SLSHARD\1"
 #define SL_SHARD_HAS_SUMS 1u
 typedef struct sl_shard_header {   /* little-endian, 64 bytes */

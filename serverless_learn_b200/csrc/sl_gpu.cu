@@ -1376,8 +1376,8 @@ int sl_shard_end(sl_handle* h, long long* n_rows) {
             h->in_len = in_len;
         }
     }
-    if (rows <= 0) {
-        // a stream without one complete row seals nothing: whatever shard was trainable before stays
+    if (rows <= 0 && h->shard_sealed && h->n_rows > 0) {
+        // a stream without one complete row never replaces a trainable shard: whatever was sealed before stays
         // (the reference acks such a stream like any other, src/worker.cc:57-60, so this is no error)
         h->in_len = 0;
         h->shard_open = false;

@@ -513,7 +513,7 @@ def test_group_of_workers_on_one_gpu_equals_sync_loop(sl, orc, W, n, F, B, varia
             r.load_shard(X, y)
         reps[0].set_option("variant", variant)
         lg = np.concatenate([sl.Replica.train_steps_group(reps, 4), sl.Replica.train_steps_group(reps, steps - 4)])
-        assert reps[0].info("path") == (6 if variant == 0 and F % 32 == 0 and F <= 1024 else 1)
+        assert reps[0].info("path") == (6 if variant == 0 and F % 16 == 0 and F <= 1024 else 1)
         for r in reps:
             assert np.array_equal(r.model(), reps[0].model())        # every replica leaves with the new model
             assert r.info("step") == steps
