@@ -59,10 +59,9 @@ struct ClArgs {
     double* loss_out;      // device [n_steps]: mean loss of every step, written by the kernel; or nullptr
     long long xstep0;      // accumulator parity of this launch's first step (continues across launches)
     // same-box data parallel: one kernel per GPU, totals summed through peer-mapped memory
-    int nranks, rank;      // nranks <= 1: single GPU
-    unsigned long long* peer_gx[8];  // rank p's cross-GPU accumulators [2][F] as mapped here (own = local)
+    int nranks, rank;      // nranks == 0: single GPU, no cross-GPU stage (1: the stage runs against itself)
+    unsigned long long* peer_gx[8];  // rank p's cross-GPU slots [2 buffers][8 ranks][F] as mapped here (own = local)
     unsigned long long* mc_gx;       // multicast alias of the same words on all ranks, or nullptr
-    unsigned long long* gxbase;      // [2][F] own accumulators' values when the previous launch ended
     double eta_over_b;     // eta / (B * ranks)
     double inv_b;          // 1 / B
     float part_limit;      // |partial| above this could overflow the accumulator word
@@ -138,8 +137,12 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
 __device__ __forceinline__ void red_add_u64_sys(unsigned long long* p, unsigned long long v) {
     asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ void multimem_red_add_u64(unsigned long long* p, unsigned long long v) {
-    asm volatile("multimem.red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// one store, delivered by the NVSwitch to the same offset in every GPU of the multicast group
+__device__ __forceinline__ void multimem_st_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
     unsigned long long v;
@@ -427,12 +430,8 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             master[i] = xact[i] ? a.model[col[i]] : 0.0;
             if (xact[i]) {
                 for (int k = 0; k < 2 * kClRep; ++k) xprev[k * fc + tl] = a.gbase[(size_t)k * F + col[i]];
-                if (a.nranks > 1) {
-                    xprev[(2 * kClRep) * fc + tl] = a.gxbase[col[i]];
-                    xprev[(2 * kClRep + 1) * fc + tl] = a.gxbase[F + col[i]];
-                }
             }
-            xsend[i] = a.nranks > 1 && xact[i] && (tl % a.ncl) == q;
+            xsend[i] = a.nranks > 0 && xact[i] && (tl % a.ncl) == q;
         }
         const uint32_t wfull_a = smem_u32(wfull), wsm_a = smem_u32(wsm);
 
@@ -510,28 +509,61 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                     T[i] += LT[i * kClRep + k];
                 }
             }
-            unsigned long long* gp[XC];
-            unsigned long long pv[XC];
             if (t == 0) cl_stamp(a, s, 3);
-            if (a.nranks > 1) {
-                // this GPU's total of a column goes to every rank's accumulator; then wait for all ranks'
+            if (a.nranks > 0) {
+                // ---- across GPUs: one 8-byte word per (rank, column) and buffer, value in the upper 57 bits and a
+                // step tag in the lower 7: the thread that forwards a column stores this GPU's total into slot
+                // [rank] of EVERY rank (one multimem.st through the NVSwitch when a multicast mapping is attached,
+                // else one store per peer over NVLink); every rank then reads the slots of all ranks in its own
+                // memory and adds them up — integers again, the same bits everywhere.  A slot's previous content
+                // is two steps older (or the zero it started with) and never carries the current tag.
+                const unsigned long long tag = (unsigned long long)((a.xstep0 + s + 1) & 127);
 #pragma unroll
                 for (int i = 0; i < XC; ++i) {
-                    gp[i] = a.peer_gx[a.rank] + (size_t)b * F + col[i];
-                    pv[i] = xact[i] ? xprev[(2 * kClRep + b) * fc + t + i * XT] : 0ull;
                     if (!xsend[i]) continue;
-                    const unsigned long long val = ((unsigned long long)T[i] << kClCntBits) + 1ull;
-                    const size_t off = (size_t)b * F + col[i];
+                    const unsigned long long word = ((unsigned long long)T[i] << 7) | tag;
+                    const size_t off = ((size_t)(b * 8 + a.rank)) * F + col[i];
                     if (a.mc_gx) {
-                        multimem_red_add_u64(a.mc_gx + off, val);
+                        multimem_st_u64(a.mc_gx + off, word);
                     } else {
-                        for (int p = 0; p < a.nranks; ++p) red_add_u64_sys(a.peer_gx[p] + off, val);
+                        for (int p = 0; p < a.nranks; ++p) st_relaxed_sys_u64(a.peer_gx[p] + off, word);
                     }
                 }
-                poll_totals<true, XC>(gp, xact, pv, T, (unsigned)a.nranks, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPeer, kPeerSpinLimit);
+                const unsigned long long* mine = a.peer_gx[a.rank] + (size_t)(b * 8) * F;
+                unsigned pend[XC];
+                long long S[XC];
 #pragma unroll
-                for (int i = 0; i < XC; ++i)
-                    if (xact[i]) xprev[(2 * kClRep + b) * fc + t + i * XT] = pv[i];
+                for (int i = 0; i < XC; ++i) {
+                    pend[i] = xact[i] ? ((1u << a.nranks) - 1u) : 0u;
+                    S[i] = 0;
+                }
+                // the columns take turns (eight loads in flight at a time: the exchange warps are short of registers)
+                uint32_t spins = 0;
+                for (;;) {
+                    bool any = false;
+#pragma unroll
+                    for (int i = 0; i < XC; ++i) {
+                        if (pend[i] == 0u) continue;
+                        unsigned long long v[8];
+#pragma unroll
+                        for (int p = 0; p < 8; ++p)
+                            if ((pend[i] >> p) & 1u) v[p] = ld_relaxed_sys_u64(mine + (size_t)p * F + col[i]);
+#pragma unroll
+                        for (int p = 0; p < 8; ++p)
+                            if ((pend[i] >> p) & 1u) {
+                                if ((v[p] & 127ull) == tag) {
+                                    S[i] += (long long)v[p] >> 7;
+                                    pend[i] &= ~(1u << p);
+                                } else {
+                                    any = true;
+                                }
+                            }
+                    }
+                    if (!any) break;
+                    if (spin_abort(spins, a.err, kErrTimeoutPeer, kPeerSpinLimit)) break;
+                }
+#pragma unroll
+                for (int i = 0; i < XC; ++i) T[i] = S[i];
             }
             // new fp32 weights to every CTA of the cluster, 16 bytes per store: the four lanes of a quad hold
             // four consecutive columns; each gathers the quad's values and serves a quarter of the CTAs
@@ -569,10 +601,6 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 a.model[col[i]] = master[i];
                 const int tl = t + i * XT;
                 for (int k = 0; k < 2 * kClRep; ++k) a.gbase[(size_t)k * F + col[i]] = xprev[k * fc + tl];
-                if (a.nranks > 1) {
-                    a.gxbase[col[i]] = xprev[(2 * kClRep) * fc + tl];
-                    a.gxbase[F + col[i]] = xprev[(2 * kClRep + 1) * fc + tl];
-                }
             }
         }
     } else {
@@ -601,7 +629,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
         const uint32_t lsend_addr = mapa_u32(smem_u32(lrecv) + (uint32_t)(((int)crank * RG + rg) * 4), 0u);
 
         const bool loss_lead = want_loss && crank == 0 && tid == 0;
-        unsigned long long* lprev = xprev + (2 * kClRep + 2) * fc;   // [3] loss accumulator values seen complete (cluster 0 only)
+        unsigned long long* lprev = xprev + (2 * kClRep) * fc;   // [3] loss accumulator values seen complete (cluster 0 only)
         int l3 = (int)(a.xstep0 % 3);
         if (loss_lead && q == 0) { lprev[0] = a.lbase[0]; lprev[1] = a.lbase[1]; lprev[2] = a.lbase[2]; }
         uint32_t slot = 0, par = 0;  // this group's ring cursor

@@ -713,7 +713,7 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     a.ycap = (a.zy_rows / v.r + v.rg - 1) / v.rg * v.r;  // passes per row group * R
     const size_t yb_b = sizeof(float) * 2 * (size_t)v.rg * a.ycap;
     const size_t slot_b = (size_t)v.rs * a.row_bytes;
-    const size_t prev_b = 8 * ((2 * slk::kClRep + 2) * (size_t)a.fc + 4);  // + the loss accumulators' values
+    const size_t prev_b = 8 * ((2 * slk::kClRep) * (size_t)a.fc + 4);  // + the loss accumulators' values
     const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + yb_b + prev_b + 8 * (2 * 32 + 6) + 512;
     if (h->smem_optin < fixed + (size_t)v.rg * slot_b) { *why = "the ring does not fit in shared memory"; return false; }
     size_t nsg = (h->smem_optin - fixed) / ((size_t)v.rg * slot_b);
@@ -744,7 +744,8 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
 }
 
 size_t xblock_gx_offset(int F) { return sizeof(uint4) * 2 * 8 * (size_t)F + 8 * 3 * (size_t)F; }
-size_t xblock_bytes_for(int F) { return xblock_gx_offset(F) + 8 * 2 * (size_t)F; }
+size_t xblock_gx_bytes(int F) { return 8 * 2 * 8 * (size_t)F; }  // K1c: [2 buffers][8 ranks][F] tagged totals
+size_t xblock_bytes_for(int F) { return xblock_gx_offset(F) + xblock_gx_bytes(F); }
 
 // Enqueues the launches (events around them); the caller synchronises.  loss_dev: device-visible
 // array of n_steps doubles the kernel writes, or nullptr.
@@ -752,7 +753,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
     const ClVariant& v = kClVariants[plan.variant];
     const int F = h->F;
     const size_t KR = slk::kClRep;
-    const size_t words = (4 * KR + 2) * (size_t)F + 8;  // gacc, gbase [2][KR][F]; gxbase [2][F]; lacc [3] + pad; lbase [3] + pad
+    const size_t words = (4 * KR) * (size_t)F + 8;  // gacc, gbase [2][KR][F]; lacc [3] + pad; lbase [3] + pad
     if (!h->cl_scratch || h->cl_scratch_F != F) {
         if (h->cl_scratch) cudaFree(h->cl_scratch);
         h->cl_scratch = nullptr;
@@ -762,7 +763,6 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
     }
     if (h->cl_dirty) {  // first use, or a launch gave up half way: start from zero (rare; costs a memset)
         CK(h, cudaMemsetAsync(h->cl_scratch, 0, 8 * words, h->stream));
-        if (h->xblock) CK(h, cudaMemsetAsync(h->xblock + xblock_gx_offset(F), 0, 8 * 2 * (size_t)F, h->stream));
         h->cl_dirty = false;
     }
     const int max_per_launch = h->opt_steps_per_launch > 0 ? (int)h->opt_steps_per_launch : kMaxStepsPerLaunch;
@@ -792,8 +792,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         a.model = h->model;
         a.gacc = h->cl_scratch;
         a.gbase = h->cl_scratch + 2 * KR * (size_t)F;
-        a.gxbase = h->cl_scratch + 4 * KR * (size_t)F;
-        a.lacc = h->cl_scratch + (4 * KR + 2) * (size_t)F;
+        a.lacc = h->cl_scratch + 4 * KR * (size_t)F;
         a.lbase = a.lacc + 4;
         a.loss_out = loss_dev ? loss_dev + done : nullptr;
         a.xstep0 = h->cl_xstep;
