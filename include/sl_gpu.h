@@ -179,6 +179,16 @@ int sl_gossip_p2p(sl_handle* initiator, sl_handle* callee);
  * forces the NCCL path; a shape the fused kernels cannot run needs NCCL too (SL_ESTATE otherwise). */
 int sl_peer_export(sl_handle* h, void* handle64);
 int sl_peer_attach(sl_handle* h, int nranks, int rank, const void* handles);
+/* NVSwitch variant for the cluster kernel (narrow rows, F <= 1024): instead of (or besides) the IPC inbox
+ * above, the caller hands in a SYMMETRIC allocation it made with its own plumbing (cuMemCreate / cuMemMap on
+ * every rank, e.g. torch.distributed._symmetric_memory): bufs[p] is rank p's buffer as mapped in this process,
+ * `multicast` the multicast address of the same allocation (cuMulticastCreate / cuMulticastBindMem) or NULL.
+ * bytes >= 128 * F, zero-filled, 8-byte aligned; the memory must outlive the handle.  With a multicast
+ * address a GPU's per-step total reaches all ranks with ONE multimem.st per column through the switch; without
+ * it, with one plain store per peer.  Only stores and loads ever touch these addresses — no TMA copy reads
+ * them.  No reference counterpart. */
+int sl_peer_attach_symmetric(sl_handle* h, int nranks, int rank, const void* const* bufs, void* multicast,
+                             size_t bytes);
 int sl_comm_unique_id(void* id128);
 int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128);
 int sl_allreduce_avg(sl_handle* h);

@@ -225,5 +225,11 @@ class Replica:
         buf = C.create_string_buffer(handles, 64 * nranks) if handles else None
         self._ck(self._L.sl_peer_attach(self._h, nranks, rank, buf))
 
+    def peer_attach_symmetric(self, nranks: int, rank: int, ptrs, multicast_ptr: int, nbytes: int):
+        """Symmetric allocation made by the caller (e.g. torch.distributed._symmetric_memory): ptrs[p] = rank p's
+        buffer as mapped here, multicast_ptr = its multicast address or 0."""
+        arr = (C.c_void_p * nranks)(*[C.c_void_p(int(p)) for p in ptrs])
+        self._ck(self._L.sl_peer_attach_symmetric(self._h, nranks, rank, arr, C.c_void_p(int(multicast_ptr) or None), nbytes))
+
     def allreduce_avg(self):
         self._ck(self._L.sl_allreduce_avg(self._h))

@@ -36,12 +36,7 @@ constexpr int kClCntBits = 7;                                  // arrivals per w
 constexpr unsigned long long kClCntMask = (1ull << kClCntBits) - 1ull;
 constexpr double kClFixInv = 1.0 / 4294967296.0;               // fixed point: 2^-32 units
 constexpr int kErrRange = 5;
-// Accumulator replicas: cluster q adds into replica q % kClRep, readers sum the replicas — fewer adders per
-// L2 word (the atomic unit serialises them), more words to poll.
-#ifndef SL_CL_KREP
-#define SL_CL_KREP 1
-#endif
-constexpr int kClRep = SL_CL_KREP;                                   // a gradient partial left the fixed-point range
+                                   // a gradient partial left the fixed-point range
 
 struct ClArgs {
     const float* X;        // [n_rows, F] row-major, resident shard
@@ -66,6 +61,7 @@ struct ClArgs {
     double inv_b;          // 1 / B
     float part_limit;      // |partial| above this could overflow the accumulator word
     int poll_delay, poll_gap;  // SM cycles before the first look at an accumulator / between looks
+    int xpoll_delay, xpoll_gap;  // the same for the all-rank words
     int* err;              // 0 = ok; set by the watchdog
     // geometry, computed on the host
     int ncl;               // clusters in the grid
@@ -156,6 +152,9 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 // diagnostics: 16 (clock64, globaltimer) pairs per CTA and step, [4 steps][grid][32].  Points 8..15 sit inside
 // the passes and perturb them (0.2 us per step at config 3): compiled in only with -DSL_CL_FINE_STAMPS=1.
+#ifndef SL_CL_XPOLL_SYS
+#define SL_CL_XPOLL_SYS 1
+#endif
 #ifndef SL_CL_FINE_STAMPS
 #define SL_CL_FINE_STAMPS 0
 #endif
@@ -236,37 +235,6 @@ __device__ __forceinline__ void poll_totals(unsigned long long* const (&p)[XC], 
     }
 }
 
-template <bool SYS, int XI>
-__device__ __forceinline__ void poll_totals_w(unsigned long long* const (&p)[XI], const bool (&act)[XI],
-                                              unsigned long long (&prev)[XI], long long (&T)[XI],
-                                              const unsigned (&want)[XI], int* err, int code, uint32_t limit) {
-    bool done[XI];
-#pragma unroll
-    for (int i = 0; i < XI; ++i) done[i] = !act[i] || want[i] == 0;
-    uint32_t spins = 0;
-    for (;;) {
-        unsigned long long v[XI];
-#pragma unroll
-        for (int i = 0; i < XI; ++i)
-            if (!done[i]) v[i] = SYS ? ld_relaxed_sys_u64(p[i]) : ld_relaxed_u64(p[i]);
-        bool all = true;
-#pragma unroll
-        for (int i = 0; i < XI; ++i) {
-            if (done[i]) continue;
-            const unsigned long long d = v[i] - prev[i];
-            if ((d & kClCntMask) == (unsigned long long)want[i]) {
-                done[i] = true;
-                prev[i] = v[i];
-                T[i] = (long long)(d - (unsigned long long)want[i]) >> kClCntBits;
-            } else {
-                all = false;
-            }
-        }
-        if (all) break;
-        if (spin_abort(spins, err, code, limit)) break;
-    }
-}
-
 // WPG warps cover a row (one float4 column chunk per thread: F <= 128*WPG); RG row groups of WPG warps
 // take R rows each per pass, from their own ring of RS-row slots; CS = CTAs per cluster; XW exchange
 // warps share the (at most 128) columns this CTA owns.  CREG > 0: the compute warpgroups take CREG
@@ -305,7 +273,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     float* red = reinterpret_cast<float*>(smem + a.off_red);            // [2][NCW][R]
     float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);            // [2][zy_rows]
     float* ybuf = reinterpret_cast<float*>(smem + a.off_yb);            // [2][RG][ycap] labels of a step's rows
-    unsigned long long* xprev = reinterpret_cast<unsigned long long*>(smem + a.off_prev);  // [4][fc] accumulator values seen complete
+    unsigned long long* xprev = reinterpret_cast<unsigned long long*>(smem + a.off_prev);  // [2][fc] accumulator values seen complete, [3] for the loss
 
     const uint32_t slot_bytes = (uint32_t)RS * (uint32_t)row_bytes;
     const long long lo = ((long long)c * a.B) / G;
@@ -429,7 +397,8 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             col[i] = (int)crank * fc + tl;
             master[i] = xact[i] ? a.model[col[i]] : 0.0;
             if (xact[i]) {
-                for (int k = 0; k < 2 * kClRep; ++k) xprev[k * fc + tl] = a.gbase[(size_t)k * F + col[i]];
+                xprev[tl] = a.gbase[col[i]];
+                xprev[fc + tl] = a.gbase[F + col[i]];
             }
             xsend[i] = a.nranks > 0 && xact[i] && (tl % a.ncl) == q;
         }
@@ -469,22 +438,19 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 bad = bad || !(fabsf(v[0]) < a.part_limit);
                 P[i] = to_fix32(v[0]);
             }
-            // local accumulators: [2 buffers][kClRep replicas][F]; this cluster adds into replica q % kClRep
-            constexpr int XI = XC * kClRep;
-            unsigned long long* lp[XI];
-            unsigned long long lpv[XI];
-            bool lact[XI];
-            long long LT[XI];
+            // this cluster's sums go into the step's accumulators; then wait until every cluster's have.  (With
+            // peers attached only the forwarding thread NEEDS this GPU's total, but letting the others skip ahead
+            // to the all-rank words made the step 1.6x slower: they then poll those words for a microsecond longer,
+            // and readers on a line slow down the stores that are on their way to it.)
+            unsigned long long* lp[XC];
+            unsigned long long lpv[XC];
+            bool lact[XC];
 #pragma unroll
             for (int i = 0; i < XC; ++i) {
-#pragma unroll
-                for (int k = 0; k < kClRep; ++k) {
-                    lp[i * kClRep + k] = a.gacc + ((size_t)(b * kClRep + k)) * F + col[i];
-                    lact[i * kClRep + k] = xact[i];
-                    lpv[i * kClRep + k] = xact[i] ? xprev[((b * kClRep + k) * fc) + t + i * XT] : 0ull;
-                    LT[i * kClRep + k] = 0;
-                }
-                if (xact[i]) red_add_u64(lp[i * kClRep + (kClRep > 1 ? q % kClRep : 0)], ((unsigned long long)P[i] << kClCntBits) + 1ull);
+                lp[i] = a.gacc + (size_t)b * F + col[i];
+                lact[i] = xact[i];
+                lpv[i] = lact[i] ? xprev[b * fc + t + i * XT] : 0ull;
+                if (xact[i]) red_add_u64(lp[i], ((unsigned long long)P[i] << kClCntBits) + 1ull);
             }
             // the compute warps hold back their next burst of shared-memory loads (pulling the next step's rows
             // into registers) until the partials have been read: the two would queue in the same pipe
@@ -492,23 +458,10 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             if (lane == 0) mbar_arrive(smem_u32(xdone));
             if (bad) atomicCAS(a.err, 0, kErrRange);
             if (t == 0) cl_stamp(a, s, 7);
-            if (kClRep == 1) {
-                poll_totals<false, XI>(lp, lact, lpv, LT, (unsigned)a.ncl, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPart, kSpinLimit);
-            } else {
-                // replica k is complete when the clusters q with q % kClRep == k have added
-                unsigned wantk[XI];
+            poll_totals<false, XC>(lp, lact, lpv, T, (unsigned)a.ncl, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPart, kSpinLimit);
 #pragma unroll
-                for (int i = 0; i < XI; ++i) wantk[i] = (unsigned)((a.ncl - (i % kClRep) + kClRep - 1) / kClRep);
-                poll_totals_w<false, XI>(lp, lact, lpv, LT, wantk, a.err, kErrTimeoutPart, kSpinLimit);
-            }
-#pragma unroll
-            for (int i = 0; i < XC; ++i) {
-#pragma unroll
-                for (int k = 0; k < kClRep; ++k) {
-                    if (xact[i]) xprev[((b * kClRep + k) * fc) + t + i * XT] = lpv[i * kClRep + k];
-                    T[i] += LT[i * kClRep + k];
-                }
-            }
+            for (int i = 0; i < XC; ++i)
+                if (lact[i]) xprev[b * fc + t + i * XT] = lpv[i];
             if (t == 0) cl_stamp(a, s, 3);
             if (a.nranks > 0) {
                 // ---- across GPUs: one 8-byte word per (rank, column) and buffer, value in the upper 57 bits and a
@@ -537,7 +490,12 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                     pend[i] = xact[i] ? ((1u << a.nranks) - 1u) : 0u;
                     S[i] = 0;
                 }
-                // the columns take turns (eight loads in flight at a time: the exchange warps are short of registers)
+                // the columns take turns (eight loads in flight at a time: the exchange warps are short of registers);
+                // nothing can have crossed NVLink before `xdelay` cycles, and every look costs the writers time
+                if (a.xpoll_delay > 0) {
+                    const long long t0 = clock64();
+                    while (clock64() - t0 < a.xpoll_delay) {}
+                }
                 uint32_t spins = 0;
                 for (;;) {
                     bool any = false;
@@ -547,7 +505,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                         unsigned long long v[8];
 #pragma unroll
                         for (int p = 0; p < 8; ++p)
-                            if ((pend[i] >> p) & 1u) v[p] = ld_relaxed_sys_u64(mine + (size_t)p * F + col[i]);
+                            if ((pend[i] >> p) & 1u) v[p] = SL_CL_XPOLL_SYS ? ld_relaxed_sys_u64(mine + (size_t)p * F + col[i]) : ld_relaxed_u64(mine + (size_t)p * F + col[i]);
 #pragma unroll
                         for (int p = 0; p < 8; ++p)
                             if ((pend[i] >> p) & 1u) {
@@ -561,9 +519,14 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                     }
                     if (!any) break;
                     if (spin_abort(spins, a.err, kErrTimeoutPeer, kPeerSpinLimit)) break;
+                    if (a.xpoll_gap > 0) {
+                        const long long t0 = clock64();
+                        while (clock64() - t0 < a.xpoll_gap) {}
+                    }
                 }
 #pragma unroll
                 for (int i = 0; i < XC; ++i) T[i] = S[i];
+                if (!SL_CL_FINE_STAMPS && t == 0) cl_stamp(a, s, 8);
             }
             // new fp32 weights to every CTA of the cluster, 16 bytes per store: the four lanes of a quad hold
             // four consecutive columns; each gathers the quad's values and serves a quarter of the CTAs
@@ -600,7 +563,8 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 if (!xact[i]) continue;
                 a.model[col[i]] = master[i];
                 const int tl = t + i * XT;
-                for (int k = 0; k < 2 * kClRep; ++k) a.gbase[(size_t)k * F + col[i]] = xprev[k * fc + tl];
+                a.gbase[col[i]] = xprev[tl];
+                a.gbase[F + col[i]] = xprev[fc + tl];
             }
         }
     } else {
@@ -629,7 +593,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
         const uint32_t lsend_addr = mapa_u32(smem_u32(lrecv) + (uint32_t)(((int)crank * RG + rg) * 4), 0u);
 
         const bool loss_lead = want_loss && crank == 0 && tid == 0;
-        unsigned long long* lprev = xprev + (2 * kClRep) * fc;   // [3] loss accumulator values seen complete (cluster 0 only)
+        unsigned long long* lprev = xprev + 2 * fc;   // [3] loss accumulator values seen complete (cluster 0 only)
         int l3 = (int)(a.xstep0 % 3);
         if (loss_lead && q == 0) { lprev[0] = a.lbase[0]; lprev[1] = a.lbase[1]; lprev[2] = a.lbase[2]; }
         uint32_t slot = 0, par = 0;  // this group's ring cursor

@@ -229,15 +229,19 @@ struct sl_handle {
     unsigned xflag_base = 0;
     long long opt_sync_path = 0;         // 0 auto (fused when attached), 1 NCCL per step
     // cluster kernel (K1c)
-    unsigned long long* cl_scratch = nullptr;  // [gacc 2F][gbase 2F][gxbase 2F][lacc 2][lbase 2]
+    unsigned long long* cl_scratch = nullptr;  // [gacc 2F][gbase 2F][lacc 3 + pad][lbase 3 + pad]
     int cl_scratch_F = 0;
     bool cl_dirty = false;               // a launch aborted: the accumulators are re-zeroed before the next one
     long long cl_xstep = 0;              // steps taken through K1c so far (accumulator parity continues across launches)
     int cl_max_clusters[16] = {};        // per variant, for the shared-memory size in cl_smem_set
     size_t cl_smem_set[16] = {};
     int cl_coop = -1;                    // cooperative + cluster launch accepted? (-1 = not tried)
-    long long opt_cl_variant = 0, opt_clusters = 0, opt_poll_delay = -1, opt_poll_gap = -1;
-    unsigned long long* mc_gx = nullptr; // multicast alias of the cross-GPU accumulators (sl_peer_attach_multicast)
+    long long opt_cl_variant = 0, opt_clusters = 0, opt_poll_delay = -1, opt_poll_gap = -1, opt_xpoll_delay = -1, opt_xpoll_gap = -1;
+    // caller-provided symmetric allocation for K1c's all-rank words (sl_peer_attach_symmetric)
+    unsigned long long* sym_buf[8] = {};
+    unsigned long long* mc_gx = nullptr; // its multicast alias (one store reaches every rank), or nullptr
+    int sym_n = 0;
+    bool ipc_attached = false;
 
     std::mutex mu;
     std::string err;
@@ -713,7 +717,7 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     a.ycap = (a.zy_rows / v.r + v.rg - 1) / v.rg * v.r;  // passes per row group * R
     const size_t yb_b = sizeof(float) * 2 * (size_t)v.rg * a.ycap;
     const size_t slot_b = (size_t)v.rs * a.row_bytes;
-    const size_t prev_b = 8 * ((2 * slk::kClRep) * (size_t)a.fc + 4);  // + the loss accumulators' values
+    const size_t prev_b = 8 * (2 * (size_t)a.fc + 4);  // + the loss accumulators' values
     const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + yb_b + prev_b + 8 * (2 * 32 + 6) + 512;
     if (h->smem_optin < fixed + (size_t)v.rg * slot_b) { *why = "the ring does not fit in shared memory"; return false; }
     size_t nsg = (h->smem_optin - fixed) / ((size_t)v.rg * slot_b);
@@ -736,6 +740,8 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     a.inv_b = 1.0 / (double)Beff;
     a.poll_delay = h->opt_poll_delay >= 0 ? (int)h->opt_poll_delay : 0;
     a.poll_gap = h->opt_poll_gap >= 0 ? (int)h->opt_poll_gap : 0;
+    a.xpoll_delay = h->opt_xpoll_delay >= 0 ? (int)h->opt_xpoll_delay : 0;
+    a.xpoll_gap = h->opt_xpoll_gap >= 0 ? (int)h->opt_xpoll_gap : 0;
     p->smem = off;
     p->variant = vi;
     p->grid = grid;
@@ -752,8 +758,7 @@ size_t xblock_bytes_for(int F) { return xblock_gx_offset(F) + xblock_gx_bytes(F)
 int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss_dev, bool fused) {
     const ClVariant& v = kClVariants[plan.variant];
     const int F = h->F;
-    const size_t KR = slk::kClRep;
-    const size_t words = (4 * KR) * (size_t)F + 8;  // gacc, gbase [2][KR][F]; lacc [3] + pad; lbase [3] + pad
+    const size_t words = 4 * (size_t)F + 8;  // gacc, gbase [2][F]; lacc [3] + pad; lbase [3] + pad
     if (!h->cl_scratch || h->cl_scratch_F != F) {
         if (h->cl_scratch) cudaFree(h->cl_scratch);
         h->cl_scratch = nullptr;
@@ -791,8 +796,8 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         a.n_steps = n;
         a.model = h->model;
         a.gacc = h->cl_scratch;
-        a.gbase = h->cl_scratch + 2 * KR * (size_t)F;
-        a.lacc = h->cl_scratch + 4 * KR * (size_t)F;
+        a.gbase = h->cl_scratch + 2 * (size_t)F;
+        a.lacc = h->cl_scratch + 4 * (size_t)F;
         a.lbase = a.lacc + 4;
         a.loss_out = loss_dev ? loss_dev + done : nullptr;
         a.xstep0 = h->cl_xstep;
@@ -802,8 +807,9 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
             a.nranks = h->peer_n;
             a.rank = h->peer_rank;
             for (int p = 0; p < h->peer_n; ++p)
-                a.peer_gx[p] = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(h->peer_base[p]) + xblock_gx_offset(F));
-            a.mc_gx = h->mc_gx;
+                a.peer_gx[p] = h->sym_n > 0 ? h->sym_buf[p]
+                                            : reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(h->peer_base[p]) + xblock_gx_offset(F));
+            a.mc_gx = h->sym_n > 0 ? h->mc_gx : nullptr;
         }
         a.dbg = done == 0 ? dbg : nullptr;
         a.dbg_step = done == 0 && dbg ? (int)h->opt_dbg_step : 0;
@@ -1066,7 +1072,7 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     std::string why;
     bool persist = !sync && h->opt_path != 2 && plan_persist(h, &plan, &why);
     bool fused = false;
-    if (sync && h->peer_n > 0 && h->opt_sync_path == 0 && h->opt_path != 2 && plan_persist(h, &plan, &why)) {
+    if (sync && h->peer_n > 0 && h->ipc_attached && h->opt_sync_path == 0 && h->opt_path != 2 && plan_persist(h, &plan, &why)) {
         const Variant& v = kVariants[plan.variant];
         fused = v.xb && (h->F + plan.args.xslice - 1) / plan.args.xslice <= plan.grid && h->peer_n <= 8;
     }
@@ -1245,6 +1251,8 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "clusters") h->opt_clusters = value;
     else if (k == "poll_delay") h->opt_poll_delay = value;
     else if (k == "poll_gap") h->opt_poll_gap = value;
+    else if (k == "xpoll_delay") h->opt_xpoll_delay = value;
+    else if (k == "xpoll_gap") h->opt_xpoll_gap = value;
     else if (k == "cl_coop") h->cl_coop = value < 0 ? -1 : (value ? 1 : 0);
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
@@ -1268,6 +1276,7 @@ long long sl_get_info(sl_handle* h, const char* key) {
     if (k == "shard_row0") return (long long)h->shard_row0;
     if (k == "nranks") return h->nranks;
     if (k == "peers") return h->peer_n;
+    if (k == "multicast") return h->sym_n > 0 && h->mc_gx ? 1 : 0;
     if (k == "num_variants") return kNumVariants;
     if (k == "num_cl_variants") return kNumClVariants;
     return SL_EINVAL;
@@ -1778,6 +1787,29 @@ int sl_peer_attach(sl_handle* h, int nranks, int rank, const void* handles) {
     h->peer_n = nranks;
     h->peer_rank = rank;
     h->xflag_base = 0;
+    h->ipc_attached = true;
+    if (h->nranks == 1) { h->nranks = nranks; h->rank = rank; }
+    return SL_OK;
+}
+
+int sl_peer_attach_symmetric(sl_handle* h, int nranks, int rank, const void* const* bufs, void* multicast, size_t bytes) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks)
+        return fail(h, SL_EINVAL, "sl_peer_attach_symmetric: 1 <= nranks <= 8 and 0 <= rank < nranks");
+    if (!bufs) return fail(h, SL_EINVAL, "bufs is NULL");
+    if (h->peer_n && (h->peer_n != nranks || h->peer_rank != rank))
+        return fail(h, SL_ESTATE, "peers already attached as rank %d of %d", h->peer_rank, h->peer_n);
+    if (bytes < xblock_gx_bytes(h->F))
+        return fail(h, SL_EINVAL, "the symmetric buffer holds %zu bytes, %zu are needed (128 * F)", bytes, xblock_gx_bytes(h->F));
+    for (int p = 0; p < nranks; ++p) {
+        if (!bufs[p] || ((uintptr_t)bufs[p] & 7)) return fail(h, SL_EINVAL, "buffer of rank %d is NULL or not 8-byte aligned", p);
+        h->sym_buf[p] = static_cast<unsigned long long*>(const_cast<void*>(bufs[p]));
+    }
+    h->mc_gx = static_cast<unsigned long long*>(multicast);
+    h->sym_n = nranks;
+    h->peer_n = nranks;
+    h->peer_rank = rank;
     if (h->nranks == 1) { h->nranks = nranks; h->rank = rank; }
     return SL_OK;
 }

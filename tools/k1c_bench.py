@@ -24,6 +24,7 @@ ap.add_argument("--loss", type=int, default=1)
 ap.add_argument("--path", type=int, default=6)
 ap.add_argument("--delay", default="-1")
 ap.add_argument("--coop", type=int, default=-1)
+ap.add_argument("--fused1", action="store_true", help="attach this replica to itself (1 rank): the cross-GPU stage runs against the own memory")
 ap.add_argument("--gap", default="-1")
 ap.add_argument("--timeline", action="store_true")
 ap.add_argument("--span", type=int, default=0, help="steps of one call whose entry/exit stamps are compared with the event time")
@@ -39,6 +40,9 @@ with Replica(a.F, a.B) as r:
     r.shard_synth(a.rows)
     r.set_option("path", a.path)
     r.set_option("cl_coop", a.coop)
+    if a.fused1:
+        r.peer_export(); r.peer_attach(1, 0, b"")
+        r.train_steps = r.train_steps_sync
     for clv in [int(x) for x in a.clv.split(",")]:
         for ncl in [int(x) for x in a.clusters.split(",")]:
           for delay in [int(x) for x in a.delay.split(",")]:
