@@ -208,13 +208,30 @@ def run_b200(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    def attach_peers(rep):
-        """Exchange the 64-byte IPC handles of the replicas' inboxes: the fused kernel then sums
-        gradients across GPUs through peer memory (NVLink), no per-step collective launch."""
+    symm_keep = []
+
+    def attach_peers(rep, width=F):
+        """Exchange the 64-byte IPC handles of the replicas' inboxes: the fused kernels then sum gradients
+        across GPUs through peer memory (NVLink), no per-step collective launch.  For narrow rows (cluster
+        kernel) the all-rank words additionally go into a symmetric allocation with a multicast address where
+        torch can make one: a GPU's total then reaches every rank with one multimem.st through the NVSwitch."""
         mine = torch.frombuffer(bytearray(rep.peer_export()), dtype=torch.uint8).cuda()
         allh = [torch.zeros(64, dtype=torch.uint8, device="cuda") for _ in range(world)]
         dist.all_gather(allh, mine)
         rep.peer_attach(world, rank, b"".join(bytes(t.cpu().numpy().tobytes()) for t in allh))
+        if width <= 1024 and width % 16 == 0 and os.environ.get("SL_BENCH_MULTICAST", "1") != "0":
+            try:
+                import torch.distributed._symmetric_memory as symm
+                nb = 128 * width
+                tbuf = symm.empty(nb, dtype=torch.uint8, device=torch.device("cuda", local_rank))
+                tbuf.zero_()
+                hdl = symm.rendezvous(tbuf, dist.group.WORLD)
+                torch.cuda.synchronize()
+                dist.barrier()
+                rep.peer_attach_symmetric(world, rank, [int(p) for p in hdl.buffer_ptrs], int(hdl.multicast_ptr or 0), nb)
+                symm_keep.append((tbuf, hdl))
+            except Exception as ex:  # no symmetric memory here: the IPC inbox (plain stores) stays
+                print(f"bench.py: symmetric memory unavailable ({ex!r}); using per-peer stores", file=sys.stderr)
 
     r = Replica(F, B, eta=ETA, device=local_rank)
     r.shard_synth(ROWS_PER_GPU, row0=shard_row0(rank))
@@ -273,6 +290,7 @@ def run_b200(args, rank, world, local_rank):
     sampler.stop_flag = True
     launches = (r.info("launches") - l0) // args.repeats
     path_used, variant_used, grid_used, slots_used = r.info("path"), r.info("variant"), r.info("grid"), r.info("ring_slots")
+    multicast_used = r.info("multicast") == 1
     k1 = max(1, (r.info("k1_launches") - k0) // args.repeats) if path_used in (1, 4, 6, 7) else max(1, launches)
     barrier()
     sampler.join(timeout=1.0)
@@ -366,7 +384,7 @@ def run_b200(args, rank, world, local_rank):
                 uid3.copy_(torch.frombuffer(bytearray(Replica.comm_unique_id()), dtype=torch.uint8))
             dist.broadcast(uid3, 0)
             rw.comm_init_rank(world, rank, bytes(uid3.cpu().numpy().tobytes()))
-            attach_peers(rw)
+            attach_peers(rw, WF)
         wstep = rw.train_steps_sync if multi else rw.train_steps
         wstep(8, want_loss=True)
         barrier()
@@ -480,6 +498,7 @@ def run_b200(args, rank, world, local_rank):
                        "kernel_path": {1: "persistent", 2: "simple", 3: "simple+nccl",
                                        4: "persistent+peer-memory exchange", 6: "cluster",
                                        7: "cluster+peer-memory exchange"}.get(path_used, "?"),
+                       "multicast": bool(multicast_used),
                        "variant": variant_used, "grid": grid_used, "ring_slots": slots_used},
             "wall_ms_per_step": 1e3 * wall_s / args.steps,
             "repeats": args.repeats, "ms_per_step_all": [1e3 * x / args.steps for x in dev_all],

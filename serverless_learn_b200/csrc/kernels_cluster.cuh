@@ -313,6 +313,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     }
     __syncthreads();
     cluster_sync_all();  // every CTA's barriers exist before anybody stores into a neighbour
+    if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp(a, a.dbg_step, 9);
 
     // ---- TMA producer: lane l owns ring slot l % nsg of row group l / nsg and fetches that slot's uses over the
     // whole launch (issuing a slot costs a thread several hundred cycles; one lane would bound the step)
@@ -585,6 +586,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             const double* m = a.model + gq * 4;
             w = make_float4((float)m[0], (float)m[1], (float)m[2], (float)m[3]);
         }
+        if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp(a, a.dbg_step, 10);
         // where this thread's gradient chunk goes: the owner CTA of its columns, one slot per (source CTA, group)
         const int owner = gv ? (gq * 4) / fc : 0;
         const uint32_t send_addr = mapa_u32(smem_u32(recv) + (uint32_t)((((int)crank * RG + rg) * fc + (gq * 4 - owner * fc)) * 4), (uint32_t)owner);
@@ -635,6 +637,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 for (int qq = 0; qq < SPB; ++qq) {
                     if (qq * RS < rc) {  // warp-uniform
                         mbar_wait(smem_u32(&gfullb[slot]), par, a.err);
+                        if (!SL_CL_FINE_STAMPS && tid == 0 && s == 0 && sb == 0 && qq == 0) cl_stamp(a, a.dbg_step, 11);
                         const uint32_t sbase = smem_u32(gring + (size_t)slot * slot_bytes);
 #pragma unroll
                         for (int rr = 0; rr < RS; ++rr) {

@@ -236,7 +236,15 @@ struct sl_handle {
     int cl_max_clusters[16] = {};        // per variant, for the shared-memory size in cl_smem_set
     size_t cl_smem_set[16] = {};
     int cl_coop = -1;                    // cooperative + cluster launch accepted? (-1 = not tried)
-    long long opt_cl_variant = 0, opt_clusters = 0, opt_poll_delay = -1, opt_poll_gap = -1, opt_xpoll_delay = -1, opt_xpoll_gap = -1;
+    // [record ev0] -> [kernel] -> [record ev1] as one instantiated graph: the three reach the GPU together, so
+    // the device does not sit between the first time stamp and the kernel waiting for the host's launch call
+    cudaGraph_t cl_graph = nullptr;
+    cudaGraphExec_t cl_gexec = nullptr;
+    cudaGraphNode_t cl_gnode = nullptr;
+    int cl_graph_ok = -1;                // -1 not tried, 0 unusable here, 1 in use
+    int cl_graph_variant = -1, cl_graph_grid = 0, cl_graph_threads = 0;
+    size_t cl_graph_smem = 0;
+    long long opt_cl_variant = 0, opt_clusters = 0, opt_poll_delay = -1, opt_poll_gap = -1, opt_xpoll_delay = -1, opt_xpoll_gap = -1, opt_cl_graph = 1;
     // caller-provided symmetric allocation for K1c's all-rank words (sl_peer_attach_symmetric)
     unsigned long long* sym_buf[8] = {};
     unsigned long long* mc_gx = nullptr; // its multicast alias (one store reaches every rank), or nullptr
@@ -753,6 +761,63 @@ size_t xblock_gx_offset(int F) { return sizeof(uint4) * 2 * 8 * (size_t)F + 8 * 
 size_t xblock_gx_bytes(int F) { return 8 * 2 * 8 * (size_t)F; }  // K1c: [2 buffers][8 ranks][F] tagged totals
 size_t xblock_bytes_for(int F) { return xblock_gx_offset(F) + xblock_gx_bytes(F); }
 
+// One launch of the cluster kernel between ev0 and ev1 as an instantiated graph (see sl_handle::cl_graph).
+// Returns false when graphs cannot carry this launch here; the caller then launches directly.
+bool cluster_graph_launch(sl_handle* h, const ClusterPlan& plan, const ClVariant& v, slk::ClArgs* a) {
+    if (h->cl_graph_ok == 0) return false;
+    void* params[] = {a};
+    cudaKernelNodeParams kp;
+    memset(&kp, 0, sizeof(kp));
+    kp.func = const_cast<void*>(v.fn);
+    kp.gridDim = dim3((unsigned)plan.grid);
+    kp.blockDim = dim3((unsigned)plan.threads);
+    kp.sharedMemBytes = (unsigned)plan.smem;
+    kp.kernelParams = params;
+    const bool same = h->cl_gexec && h->cl_graph_variant == plan.variant && h->cl_graph_grid == plan.grid &&
+                      h->cl_graph_threads == plan.threads && h->cl_graph_smem == plan.smem;
+    auto give_up = [&]() {
+        cudaGetLastError();
+        if (h->cl_gexec) cudaGraphExecDestroy(h->cl_gexec);
+        if (h->cl_graph) cudaGraphDestroy(h->cl_graph);
+        h->cl_gexec = nullptr;
+        h->cl_graph = nullptr;
+        h->cl_graph_ok = 0;
+        return false;
+    };
+    if (!same) {
+        if (h->cl_gexec) cudaGraphExecDestroy(h->cl_gexec);
+        if (h->cl_graph) cudaGraphDestroy(h->cl_graph);
+        h->cl_gexec = nullptr;
+        h->cl_graph = nullptr;
+        cudaGraphNode_t n0 = nullptr, n2 = nullptr;
+        if (cudaGraphCreate(&h->cl_graph, 0) != cudaSuccess) return give_up();
+        if (cudaGraphAddEventRecordNode(&n0, h->cl_graph, nullptr, 0, h->ev0) != cudaSuccess) return give_up();
+        if (cudaGraphAddKernelNode(&h->cl_gnode, h->cl_graph, &n0, 1, &kp) != cudaSuccess) return give_up();
+        cudaLaunchAttributeValue val;
+        memset(&val, 0, sizeof(val));
+        val.clusterDim.x = (unsigned)v.cs;
+        val.clusterDim.y = 1;
+        val.clusterDim.z = 1;
+        if (cudaGraphKernelNodeSetAttribute(h->cl_gnode, cudaLaunchAttributeClusterDimension, &val) != cudaSuccess) return give_up();
+        if (h->cl_coop != 0) {
+            memset(&val, 0, sizeof(val));
+            val.cooperative = 1;
+            if (cudaGraphKernelNodeSetAttribute(h->cl_gnode, cudaLaunchAttributeCooperative, &val) != cudaSuccess) cudaGetLastError();
+        }
+        if (cudaGraphAddEventRecordNode(&n2, h->cl_graph, &h->cl_gnode, 1, h->ev1) != cudaSuccess) return give_up();
+        if (cudaGraphInstantiate(&h->cl_gexec, h->cl_graph, 0) != cudaSuccess) return give_up();
+        h->cl_graph_variant = plan.variant;
+        h->cl_graph_grid = plan.grid;
+        h->cl_graph_threads = plan.threads;
+        h->cl_graph_smem = plan.smem;
+    } else if (cudaGraphExecKernelNodeSetParams(h->cl_gexec, h->cl_gnode, &kp) != cudaSuccess) {
+        return give_up();
+    }
+    if (cudaGraphLaunch(h->cl_gexec, h->stream) != cudaSuccess) return give_up();
+    h->cl_graph_ok = 1;
+    return true;
+}
+
 // Enqueues the launches (events around them); the caller synchronises.  loss_dev: device-visible
 // array of n_steps doubles the kernel writes, or nullptr.
 int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss_dev, bool fused) {
@@ -784,7 +849,9 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         CK(h, cudaMemsetAsync(h->dbg, 0, dw * 8, h->stream));
         dbg = h->dbg;
     }
-    CK(h, cudaEventRecord(h->ev0, h->stream));
+    const bool one_graph = n_steps <= max_per_launch && !dbg && h->opt_cl_graph != 0;
+    bool in_graph = false;
+    if (!one_graph) CK(h, cudaEventRecord(h->ev0, h->stream));
     int done = 0;
     while (done < n_steps) {
         const int n = std::min(max_per_launch, n_steps - done);
@@ -813,6 +880,16 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         }
         a.dbg = done == 0 ? dbg : nullptr;
         a.dbg_step = done == 0 && dbg ? (int)h->opt_dbg_step : 0;
+        if (one_graph && cluster_graph_launch(h, plan, v, &a)) {
+            in_graph = true;
+            h->launches++;
+            h->k1_launches++;
+            h->step += n;
+            h->cl_xstep += n;
+            done += n;
+            continue;
+        }
+        if (one_graph && done == 0) CK(h, cudaEventRecord(h->ev0, h->stream));
         void* params[] = {&a};
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof(cfg));
@@ -852,7 +929,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         h->cl_xstep += n;
         done += n;
     }
-    CK(h, cudaEventRecord(h->ev1, h->stream));
+    if (!in_graph) CK(h, cudaEventRecord(h->ev1, h->stream));
     h->path_used = fused ? 7 : 6;
     h->variant_used = 100 + plan.variant + 1;
     h->grid_used = plan.grid;
@@ -1200,6 +1277,8 @@ int sl_destroy(sl_handle* h) {
     cudaFree(h->acc); cudaFree(h->counter); cudaFree(h->wmaster); cudaFree(h->w32buf); cudaFree(h->d_loss); cudaFree(h->loss_fix);
     cudaFree(h->dbg);
     cudaFree(h->cl_scratch);
+    if (h->cl_gexec) cudaGraphExecDestroy(h->cl_gexec);
+    if (h->cl_graph) cudaGraphDestroy(h->cl_graph);
     for (int p = 0; p < h->peer_n; ++p)
         if (p != h->peer_rank && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
     cudaFree(h->xblock);
@@ -1253,6 +1332,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "poll_gap") h->opt_poll_gap = value;
     else if (k == "xpoll_delay") h->opt_xpoll_delay = value;
     else if (k == "xpoll_gap") h->opt_xpoll_gap = value;
+    else if (k == "cl_graph") h->opt_cl_graph = value;
     else if (k == "cl_coop") h->cl_coop = value < 0 ? -1 : (value ? 1 : 0);
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;
@@ -1277,6 +1357,7 @@ long long sl_get_info(sl_handle* h, const char* key) {
     if (k == "nranks") return h->nranks;
     if (k == "peers") return h->peer_n;
     if (k == "multicast") return h->sym_n > 0 && h->mc_gx ? 1 : 0;
+    if (k == "cl_graph") return h->cl_graph_ok;
     if (k == "num_variants") return kNumVariants;
     if (k == "num_cl_variants") return kNumClVariants;
     return SL_EINVAL;

@@ -24,6 +24,7 @@ ap.add_argument("--loss", type=int, default=1)
 ap.add_argument("--path", type=int, default=6)
 ap.add_argument("--delay", default="-1")
 ap.add_argument("--coop", type=int, default=-1)
+ap.add_argument("--graph", type=int, default=1)
 ap.add_argument("--fused1", action="store_true", help="attach this replica to itself (1 rank): the cross-GPU stage runs against the own memory")
 ap.add_argument("--gap", default="-1")
 ap.add_argument("--timeline", action="store_true")
@@ -40,6 +41,7 @@ with Replica(a.F, a.B) as r:
     r.shard_synth(a.rows)
     r.set_option("path", a.path)
     r.set_option("cl_coop", a.coop)
+    r.set_option("cl_graph", a.graph)
     if a.fused1:
         r.peer_export(); r.peer_attach(1, 0, b"")
         r.train_steps = r.train_steps_sync
@@ -76,6 +78,8 @@ with Replica(a.F, a.B) as r:
                 e0 = ent.min()
                 print(f"span of a {a.span}-step call: event time {ms * 1e3:.2f} us; kernel entry spread {ent.max() - e0} ns, "
                       f"exit {ext.min() - e0}..{ext.max() - e0} ns after the first entry")
+                print(f"  cluster barrier passed {np.median(t[0, :, 9, 1]) - e0:.0f}  weights loaded {np.median(t[0, :, 10, 1]) - e0:.0f}  "
+                      f"first rows landed {np.median(t[0, :, 11, 1]) - e0:.0f} (median ns after the first entry)")
                 for s_ in range(min(4, a.span)):
                     print(f"  step {s_}: P0 {np.median(t[s_, :, 0, 1]) - e0:.0f}  P5 {np.median(t[s_, :, 5, 1]) - e0:.0f}  P1 {np.median(t[s_, :, 1, 1]) - e0:.0f}  "
                           f"P7 {np.median(t[s_, :, 7, 1]) - e0:.0f}  P3 {np.median(t[s_, :, 3, 1]) - e0:.0f}  P4 {np.median(t[s_, :, 4, 1]) - e0:.0f} (median ns after the first entry)")
