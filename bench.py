@@ -192,6 +192,22 @@ def run_b200(args, rank, world, local_rank):
 
     torch.cuda.set_device(local_rank)
     multi = world > 1
+    numa_note = None
+    if multi:
+        # every rank's pinned host buffers (first touch) and its copy-issuing thread on the CPUs next to its GPU:
+        # eight ranks streaming from one socket's memory halve each other's host-to-device rate
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            hnd = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+            words = pynvml.nvmlDeviceGetCpuAffinity(hnd, (os.cpu_count() + 63) // 64)
+            cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1}
+            cpus &= os.sched_getaffinity(0)
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+                numa_note = f"rank bound to the {len(cpus)} CPUs nearest its GPU"
+        except Exception as ex:
+            numa_note = f"no CPU binding ({ex!r})"
     if multi:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -513,7 +529,7 @@ def run_b200(args, rank, world, local_rank):
                          "launches": k1},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                     "d2h_bytes_per_step": 8, "steps": e2e_steps, "last_loss": float(loss),
-                    "pcie_gbs": world * e2e_steps * nbytes / e2e_s / 1e9 / world,
+                    "pcie_gbs": world * e2e_steps * nbytes / e2e_s / 1e9 / world, "host_binding": numa_note,
                     "note": "every sample crosses PCIe once and is used once: 4,100 B per sample bounds this leg at "
                             "host-to-device bandwidth / 4100, whatever the kernel does"},
             "e2e_resident": {"value": world * res_steps * B / res_s, "unit": UNIT,

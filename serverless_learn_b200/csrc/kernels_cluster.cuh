@@ -55,7 +55,7 @@ struct ClArgs {
     long long xstep0;      // accumulator parity of this launch's first step (continues across launches)
     // same-box data parallel: one kernel per GPU, totals summed through peer-mapped memory
     int nranks, rank;      // nranks == 0: single GPU, no cross-GPU stage (1: the stage runs against itself)
-    unsigned long long* peer_gx[8];  // rank p's cross-GPU slots [2 buffers][8 ranks][F] as mapped here (own = local)
+    unsigned long long* peer_gx[8];  // rank p's all-rank words [2 buffers][F][8 ranks] as mapped here (own = local)
     unsigned long long* mc_gx;       // multicast alias of the same words on all ranks, or nullptr
     double eta_over_b;     // eta / (B * ranks)
     double inv_b;          // 1 / B
@@ -140,6 +140,11 @@ __device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsign
 __device__ __forceinline__ void multimem_st_u64(unsigned long long* p, unsigned long long v) {
     asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+__device__ __forceinline__ ulonglong2 ld_relaxed_sys_v2u64(const unsigned long long* p) {
+    ulonglong2 v;
+    asm volatile("ld.relaxed.sys.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
     unsigned long long v;
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -152,9 +157,6 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 // diagnostics: 16 (clock64, globaltimer) pairs per CTA and step, [4 steps][grid][32].  Points 8..15 sit inside
 // the passes and perturb them (0.2 us per step at config 3): compiled in only with -DSL_CL_FINE_STAMPS=1.
-#ifndef SL_CL_XPOLL_SYS
-#define SL_CL_XPOLL_SYS 1
-#endif
 #ifndef SL_CL_FINE_STAMPS
 #define SL_CL_FINE_STAMPS 0
 #endif
@@ -476,14 +478,14 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 for (int i = 0; i < XC; ++i) {
                     if (!xsend[i]) continue;
                     const unsigned long long word = ((unsigned long long)T[i] << 7) | tag;
-                    const size_t off = ((size_t)(b * 8 + a.rank)) * F + col[i];
+                    const size_t off = ((size_t)b * F + col[i]) * 8 + a.rank;  // [buffer][column][rank]: a column's eight words share 64 bytes
                     if (a.mc_gx) {
                         multimem_st_u64(a.mc_gx + off, word);
                     } else {
                         for (int p = 0; p < a.nranks; ++p) st_relaxed_sys_u64(a.peer_gx[p] + off, word);
                     }
                 }
-                const unsigned long long* mine = a.peer_gx[a.rank] + (size_t)(b * 8) * F;
+                const unsigned long long* mine = a.peer_gx[a.rank] + (size_t)b * F * 8;
                 unsigned pend[XC];
                 long long S[XC];
 #pragma unroll
@@ -505,8 +507,12 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                         if (pend[i] == 0u) continue;
                         unsigned long long v[8];
 #pragma unroll
-                        for (int p = 0; p < 8; ++p)
-                            if ((pend[i] >> p) & 1u) v[p] = SL_CL_XPOLL_SYS ? ld_relaxed_sys_u64(mine + (size_t)p * F + col[i]) : ld_relaxed_u64(mine + (size_t)p * F + col[i]);
+                        for (int p = 0; p < 8; p += 2)   // two ranks' words per 16-byte load
+                            if ((pend[i] >> p) & 3u) {
+                                const ulonglong2 w2 = ld_relaxed_sys_v2u64(mine + (size_t)col[i] * 8 + p);
+                                v[p] = w2.x;
+                                v[p + 1] = w2.y;
+                            }
 #pragma unroll
                         for (int p = 0; p < 8; ++p)
                             if ((pend[i] >> p) & 1u) {
