@@ -124,6 +124,7 @@ constexpr int kErrTimeoutW = 3;
 #define SL_POLL_SLEEP 0
 #endif
 constexpr int kErrTimeoutPeer = 4;
+constexpr int kErrRange = 5;   // a gradient partial left the fixed-point range (reported as SL_EINVAL, not as a timeout)
 __device__ __forceinline__ bool spin_abort(uint32_t& spins, int* err, int code,
                                            uint32_t limit = kSpinLimit) {
     ++spins;
@@ -266,14 +267,10 @@ struct LrArgs {
     int xslice;            // elements per slice (32 in lr_persist_kernel)
     int tma_chunk;         // bytes per bulk copy (a row block is fetched as several copies on one mbarrier)
     int dbg_skip;          // diagnostics: K1w skips the per-row maths (measures the bare TMA ring rate)
-    int poll_pause;        // SM cycles the exchange thread waits after its bump before it starts polling
     int block_rows;        // K1w: 1 = a CTA takes a contiguous block of the minibatch instead of every G-th row
-    int relaxed_signal;    // experiment: bump the arrival counter with a relaxed red after the bulk reduction completed
-    int rotate_reduce;     // 1: CTA-dependent start line of the bulk reduction
-    int hold_refills;      // 1: the producer re-arms slots only after the step's reduction is released
-    int direct_total;      // 1: threads read the gradient total straight from L2 instead of a TMA load into smem
     unsigned long long* loss_fix;  // device [n_steps] s64 fixed-point loss sums (zero at launch) or nullptr
     double eta_over_b;
+    float fix_limit;       // |gradient partial| at or above this could overflow the 64-bit fixed-point sums
     int* err;              // 0 = ok; set by the watchdog
     // geometry, computed on the host
     int Fp;                // accumulator vector length (= F)
@@ -380,6 +377,12 @@ __device__ __forceinline__ void red_add_u64(unsigned long long* p, unsigned long
 }
 // exact: scaling by 2^36 does not round in fp32, the conversion rounds once
 __device__ __forceinline__ long long to_fix(float v) { return __float2ll_rn(v * 68719476736.0f); }
+// Sums of these integers must fit 64 bits: a partial beyond `limit` (2^27 over the number of partials that
+// are added up; NaN too) is reported through the watchdog word instead of wrapping silently.
+__device__ __forceinline__ void check_fix_range(const float4& t, float limit, int* err) {
+    const float m = fmaxf(fmaxf(fabsf(t.x), fabsf(t.y)), fmaxf(fabsf(t.z), fabsf(t.w)));
+    if (!(m < limit)) atomicCAS(err, 0, kErrRange);
+}
 
 template <int CH, int R, int RS, int NCW, bool XB, int WM>
 __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrArgs a) {
@@ -403,7 +406,6 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
     uint64_t* empty = full + a.ns;                                     // [ns]
     uint64_t* gfull = empty + a.ns;                                    // [1] gradient staged
     uint64_t* wfull = gfull + 1;                                       // [1] total received
-    uint64_t* rgo = wfull + 1;                                         // [1] reduction released (gates refills)
     float* red = reinterpret_cast<float*>(smem + a.off_red);          // [2][NCW][R]
     float2* zy = reinterpret_cast<float2*>(smem + a.off_zy);          // [2][zy_rows] (z, y) per row
     float* gsm = reinterpret_cast<float*>(smem + a.off_gsm);          // [RG-1][F]
@@ -443,7 +445,6 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             mbar_init(smem_u32(gfull), XB ? comb_warps : comb_threads);
         }
         mbar_init(smem_u32(wfull), 1);
-        mbar_init(smem_u32(rgo), 1);
         fence_mbar_init();
     }
     __syncthreads();
@@ -454,20 +455,9 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
             const uint64_t pol = policy_evict_first();
             uint32_t slot = 0, phase = 0;
             long long mb = mb0;
-            // hold_refills: a slot freed during step t is re-armed only once step t's gradient
-            // reduction has been released — the HBM refill burst otherwise shares L2 with the
-            // 148 CTAs' reductions and stretches the release by ~0.8 us
             uint32_t pos = 0;        // position of the slot being issued in this CTA's stream
-            int gated = -1;          // last step whose release has been awaited
             for (int s = 0; s < a.n_steps; ++s) {
                 for (int q = 0; q < nsl_c; ++q, ++pos) {
-                    if (a.hold_refills && pos >= (uint32_t)ns) {
-                        const int freed_in = (int)((pos - (uint32_t)ns) / (uint32_t)nsl_c);
-                        while (gated < freed_in) {
-                            ++gated;
-                            mbar_wait(smem_u32(rgo), (uint32_t)gated & 1u, a.err);
-                        }
-                    }
                     mbar_wait(smem_u32(&empty[slot]), phase ^ 1u, a.err);
                     const int rc = min(RS, nrows_c - q * RS);
                     const uint32_t fb = smem_u32(&full[slot]);
@@ -510,45 +500,22 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                 dbg_stamp(a, s, 6);
                 if (XB) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    if (a.rotate_reduce) {
-                        // every CTA of a replica starts its reduction at a different line, so the
-                        // CTAs do not walk the accumulator's lines in lock step
-                        const uint32_t bytes = (uint32_t)Fp * 8u;
-                        const uint32_t lines = bytes / 128u;
-                        const uint32_t per = (uint32_t)(G + KREP - 1) / (uint32_t)KREP;
-                        const uint32_t off = lines ? (((uint32_t)(c / KREP) * lines / per) % lines) * 128u : 0u;
-                        unsigned long long* dst = buf + (size_t)(c % KREP) * Fp;
-                        if (off < bytes)
-                            bulk_reduce_add_u64(reinterpret_cast<unsigned char*>(dst) + off,
-                                                smem_u32(gout) + off, bytes - off);
-                        if (off > 0) bulk_reduce_add_u64(dst, smem_u32(gout), off);
-                    } else {
-                        bulk_reduce_add_u64(buf + (size_t)(c % KREP) * Fp, smem_u32(gout),
-                                            (uint32_t)Fp * 8u);
-                    }
+                    bulk_reduce_add_u64(buf + (size_t)(c % KREP) * Fp, smem_u32(gout), (uint32_t)Fp * 8u);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
                     dbg_stamp(a, s, 7);
                     asm volatile("fence.proxy.async;" ::: "memory");
                 }
-                if (XB && a.relaxed_signal)
-                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(counter), "r"(1u) : "memory");
-                else
-                    red_release_add_u32(counter, 1u);
-                mbar_arrive(smem_u32(rgo));  // the producer may refill what step s freed
+                red_release_add_u32(counter, 1u);
                 dbg_stamp(a, s, 3);
                 const unsigned want = (unsigned)G * (unsigned)(s + 1);
                 uint32_t spins = 0;
-                if (a.poll_pause > 0) {  // the first bumps cannot complete the count: do not poll yet
-                    const long long t0 = clock64();
-                    while (clock64() - t0 < a.poll_pause) {}
-                }
                 while ((int)(ld_relaxed_u32(counter) - want) < 0) {
                     if (spin_abort(spins, a.err, kErrTimeoutPart)) break;
                 }
                 asm volatile("fence.acq_rel.gpu;" ::: "memory");
                 if (a.nranks == 0) {
-                    if (XB && !a.direct_total) {
+                    if (XB) {
                         asm volatile("fence.proxy.async;" ::: "memory");
                         const uint32_t wb = smem_u32(wfull);
                         mbar_arrive_expect_tx(wb, (uint32_t)acc_stride * 8u);
@@ -711,22 +678,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
         for (int ch = 0; ch < CH; ++ch) {
             if (!gv[ch]) continue;
             long long t[4] = {0, 0, 0, 0};
-            if (XB && a.direct_total && a.nranks == 0) {
-                ulonglong2 u[4], v[4];  // KREP <= 4; all loads in flight, one L2 round trip
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (k < KREP) {
-                        const unsigned long long* p = buf + (size_t)k * Fp + gq[ch] * 4;
-                        u[k] = ld_relaxed_v2u64(p);
-                        v[k] = ld_relaxed_v2u64(p + 2);
-                    }
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (k < KREP) {
-                        t[0] += (long long)u[k].x; t[1] += (long long)u[k].y;
-                        t[2] += (long long)v[k].x; t[3] += (long long)v[k].y;
-                    }
-            } else if (XB) {
+            if (XB) {
                 const int nrep = a.nranks > 0 ? 1 : KREP;  // multi-GPU: gin holds the one all-rank total
                 for (int k = 0; k < nrep; ++k) {
                     const longlong2* p = reinterpret_cast<const longlong2*>(gin + (size_t)k * Fp + gq[ch] * 4);
@@ -923,6 +875,7 @@ __global__ void __launch_bounds__((NCW + 2) * 32, 1) lr_persist_kernel(const LrA
                     gqc = gq[ch];
                     t = g[ch];
                 }
+                check_fix_range(t, a.fix_limit, a.err);
                 if (XB) {
                     longlong2* p = reinterpret_cast<longlong2*>(gout + gqc * 4);
                     p[0] = make_longlong2(to_fix(t.x), to_fix(t.y));

@@ -35,8 +35,6 @@ namespace slk {
 constexpr int kClCntBits = 7;                                  // arrivals per word: up to 127 adders
 constexpr unsigned long long kClCntMask = (1ull << kClCntBits) - 1ull;
 constexpr double kClFixInv = 1.0 / 4294967296.0;               // fixed point: 2^-32 units
-constexpr int kErrRange = 5;
-                                   // a gradient partial left the fixed-point range
 
 struct ClArgs {
     const float* X;        // [n_rows, F] row-major, resident shard

@@ -127,10 +127,7 @@ __global__ void __launch_bounds__((NCW + 1 + (NM + LPW - 1) / LPW) * 32, 1) lr_i
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
                 asm volatile("fence.proxy.async;" ::: "memory");
-                if (a.relaxed_signal)  // experiment, see DESIGN.md §4
-                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(counter), "r"(1u) : "memory");
-                else
-                    red_release_add_u32(counter, 1u);
+                red_release_add_u32(counter, 1u);
                 const unsigned want = (unsigned)G * (unsigned)(s + 1);
                 uint32_t spins = 0;
                 while ((int)(ld_relaxed_u32(counter) - want) < 0) {
@@ -287,6 +284,7 @@ __global__ void __launch_bounds__((NCW + 1 + (NM + LPW - 1) / LPW) * 32, 1) lr_i
             // hand the gradient of (s, m) to model m's exchange warp
             if (gv) {
                 longlong2* p = reinterpret_cast<longlong2*>(gout + (size_t)m * Fp + tid * 4);
+                check_fix_range(g, a.fix_limit, a.err);
                 p[0] = make_longlong2(to_fix(g.x), to_fix(g.y));
                 p[1] = make_longlong2(to_fix(g.z), to_fix(g.w));
             }

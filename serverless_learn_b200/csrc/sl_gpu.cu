@@ -93,9 +93,9 @@ const Variant kVariants[] = {
     SL_VARIANT(1, 8, 4, 16, 1, 0),    // 4: F <= 2048
     SL_VARIANT(2, 8, 4, 8, 1, 0),     // 5: F <= 2048
     SL_VARIANT(4, 4, 2, 8, 1, 0),     // 6: F <= 4096
-    SL_VARIANT(4, 4, 2, 16, 0, 0),    // 7: F <= 8192, per-element exchange
-    SL_VARIANT(8, 1, 1, 16, 0, 1),    // 8: F <= 16384, weights in shared memory
-    SL_VARIANT(8, 2, 1, 8, 0, 1),     // 9: F <= 8192,  weights in shared memory
+    Variant{4, 4, 2, 16, 0, 0, 0, nullptr},   // 7-9: retired (the in-kernel wide modes that lr_wide_kernel replaced;
+    Variant{8, 1, 1, 16, 0, 1, 0, nullptr},   //      numbers kept so that the later entries keep theirs)
+    Variant{8, 2, 1, 8, 0, 1, 0, nullptr},
     SL_VARIANT(4, 4, 4, 14, 1, 2),    // 10: F <= 1024 as 7 row groups of 2 warps x 4 rows: 28 rows in one pass
     SL_WIDE(10, 14, 1, 1),            // 11: F <= 17920, wide-row kernel, 14+1 warps = 128 registers/thread
     SL_WIDE(5, 14, 1, 1),             // 12: F <= 8960,  wide-row kernel
@@ -208,8 +208,7 @@ struct sl_handle {
 
     // options
     long long opt_grid = 0, opt_variant = 0, opt_path = 0, opt_steps_per_launch = 0;
-    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_direct = 0, opt_hold = 0, opt_rotate = 0, opt_persist_l2 = 0, opt_poll_pause = 0, opt_dbg_skip = 0, opt_tma_chunk = 0, opt_relaxed_signal = 0, opt_block_rows = 0, opt_multi_mode = 0, opt_multi_lpw = 0;
-    bool l2_window_set = false;
+    long long opt_dbg_step = -1, opt_ring = 0, opt_krep = 0, opt_dbg_skip = 0, opt_tma_chunk = 0, opt_block_rows = 0, opt_multi_mode = 0, opt_multi_lpw = 0;
     unsigned long long* loss_fix = nullptr;
     unsigned long long* dbg = nullptr;
     size_t dbg_words = 0;
@@ -256,6 +255,15 @@ struct sl_handle {
 };
 
 namespace {
+
+int fail(sl_handle* h, int code, const char* fmt, ...);
+// what the kernels left in the watchdog word: a range error is the caller's data, anything else a wait that gave up
+int fail_watchdog(sl_handle* h, int code) {
+    if (code == slk::kErrRange)
+        return fail(h, SL_EINVAL, "a gradient partial left the fixed-point range of the exchange (features too large for "
+                    "the 64-bit sums, or not finite): the model is not usable");
+    return fail(h, SL_ETIMEOUT, "in-kernel wait timed out (watchdog code %d)", code);
+}
 
 int fail(sl_handle* h, int code, const char* fmt, ...) {
     char buf[512];
@@ -369,6 +377,7 @@ bool plan_persist(sl_handle* h, PersistPlan* p, std::string* why) {
     int vi = -1;
     if (h->opt_variant > 0 && h->opt_variant <= kNumVariants) {
         vi = (int)h->opt_variant - 1;
+        if (!kVariants[vi].fn) { *why = "this variant number is retired"; return false; }
         if (granules > variant_granules(kVariants[vi])) {
             *why = "requested variant too narrow for F";
             return false;
@@ -524,20 +533,6 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
         const long long cap = ((1ll << 31) - 1 - plan.args.ns) / std::max(1ll, rows_per_cta);
         max_per_launch = (int)std::max(1ll, std::min<long long>(max_per_launch, cap));
     }
-    if (h->opt_persist_l2 && !h->l2_window_set) {
-        // keep the gradient accumulators resident in L2 while 2+ TB/s of rows stream through it
-        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 4u << 20);
-        cudaStreamAttrValue av;
-        memset(&av, 0, sizeof(av));
-        av.accessPolicyWindow.base_ptr = h->acc;
-        av.accessPolicyWindow.num_bytes = h->acc_bytes;
-        av.accessPolicyWindow.hitRatio = 1.0f;
-        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-        cudaError_t e = cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av);
-        if (e != cudaSuccess) cudaGetLastError();
-        h->l2_window_set = true;
-    }
     int done = 0;
     *h->h_err = 0;
     const int np = plan.args.npart > 1 ? plan.args.npart : 1;
@@ -565,16 +560,12 @@ int run_persist(sl_handle* h, const PersistPlan& plan, int n_steps, bool want_lo
             CK(h, cudaMemsetAsync(h->acc, 0, 8 * (size_t)3 * a.krep * a.Fp * np, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 256, h->stream));
         a.eta_over_b = h->eta / (double)a.B;
+        a.fix_limit = 134217728.0f / (float)((long long)plan.grid * (kVariants[plan.variant].kind == 1 ? kVariants[plan.variant].r : 1) * (fused_sync ? std::max(1, h->peer_n) : 1));
         for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; a.pmodel[k] = h->pmodel[k]; }
         a.loss_stride = n_steps;
-        a.hold_refills = h->opt_hold != 0 ? 1 : 0;
-        a.rotate_reduce = h->opt_rotate != 0 ? 1 : 0;
-        a.poll_pause = (int)h->opt_poll_pause;
-        a.relaxed_signal = h->opt_relaxed_signal != 0 ? 1 : 0;
         a.block_rows = h->opt_block_rows != 0 ? 1 : 0;
         a.dbg_skip = h->opt_dbg_skip != 0 ? 1 : 0;
         a.tma_chunk = h->opt_tma_chunk > 0 ? (int)((h->opt_tma_chunk + 15) / 16 * 16) : (1 << 20);
-        a.direct_total = (h->opt_direct != 0 && kVariants[plan.variant].ws == 0 && kVariants[plan.variant].kind == 0 && plan.args.krep <= 4) ? 1 : 0;
         if (fused_sync) {
             a.nranks = h->peer_n;
             a.rank = h->peer_rank;
@@ -1049,9 +1040,9 @@ int run_interleaved(sl_handle* h, int n_steps, bool want_loss) {
         a.loss_fix = want_loss ? h->loss_fix + done : nullptr;
         a.loss_stride = n_steps;
         a.eta_over_b = h->eta / (double)h->B;
+        a.fix_limit = 134217728.0f / (float)grid;
         a.err = h->d_err;
         a.tma_chunk = 1 << 20;
-        a.relaxed_signal = h->opt_relaxed_signal != 0 ? 1 : 0;
         for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; a.pmodel[k] = h->pmodel[k]; }
         CK(h, cudaMemsetAsync(h->acc, 0, need, h->stream));
         CK(h, cudaMemsetAsync(h->counter, 0, 256, h->stream));
@@ -1114,12 +1105,8 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
             if (*h->h_err != 0) {
                 const int code = *h->h_err;
                 *h->h_err = 0;
-                if (code == slk::kErrRange)
-                    return fail(h, SL_EINVAL, "a gradient partial left the fixed-point range (|sum| must stay below %g per "
-                                "row group and step): features too large for this kernel, the model is not usable",
-                                (double)cp.args.part_limit);
-                h->cl_dirty = true;
-                return fail(h, SL_ETIMEOUT, "in-kernel wait timed out (watchdog code %d)", code);
+                if (code != slk::kErrRange) h->cl_dirty = true;
+                return fail_watchdog(h, code);
             }
             if (loss_out) memcpy(loss_out, h->h_loss, sizeof(double) * nloss);
             return SL_OK;
@@ -1140,7 +1127,7 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
         if (*h->h_err != 0) {
             const int code = *h->h_err;
             *h->h_err = 0;
-            return fail(h, SL_ETIMEOUT, "in-kernel wait timed out (watchdog code %d)", code);
+            return fail_watchdog(h, code);
         }
         if (loss_out) memcpy(loss_out, h->h_loss, sizeof(double) * nloss);
         return SL_OK;
@@ -1190,7 +1177,7 @@ int train_impl(sl_handle* h, int n_steps, double* loss_out, bool sync) {
     if (*h->h_err != 0) {
         const int code = *h->h_err;
         *h->h_err = 0;
-        return fail(h, SL_ETIMEOUT, "in-kernel wait timed out (watchdog code %d)", code);
+        return fail_watchdog(h, code);
     }
     if (loss_out) memcpy(loss_out, h->h_loss, sizeof(double) * nloss);
     return SL_OK;
@@ -1314,15 +1301,9 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "debug_timeline") h->opt_dbg_step = value;
     else if (k == "ring_slots") h->opt_ring = value;
     else if (k == "krep") h->opt_krep = value;
-    else if (k == "direct_total") h->opt_direct = value;
-    else if (k == "hold_refills") h->opt_hold = value;
-    else if (k == "rotate_reduce") h->opt_rotate = value;
-    else if (k == "persist_l2") h->opt_persist_l2 = value;
-    else if (k == "relaxed_signal") h->opt_relaxed_signal = value;
     else if (k == "block_rows") h->opt_block_rows = value;
     else if (k == "multi_mode") h->opt_multi_mode = value;
     else if (k == "multi_lpw") h->opt_multi_lpw = value;
-    else if (k == "poll_pause") h->opt_poll_pause = value;
     else if (k == "debug_skip_compute") h->opt_dbg_skip = value;
     else if (k == "tma_chunk") h->opt_tma_chunk = value;
     else if (k == "sync_path") h->opt_sync_path = value;

@@ -178,7 +178,7 @@ def test_lr_golden_cases(sl, orc, name, path):
     assert w_err(wg, GOLD[f"{name}_w"]) <= W_TOL
 
 
-@pytest.mark.parametrize("variant", list(range(1, 30)))
+@pytest.mark.parametrize("variant", [v for v in range(1, 30) if v not in (7, 8, 9)])   # 7-9 are retired
 @pytest.mark.parametrize("shape", [(300, 64, 48), (2000, 1024, 256), (700, 260, 100)])
 def test_lr_all_variants(sl, orc, variant, shape):
     n, F, B = shape
@@ -188,8 +188,8 @@ def test_lr_all_variants(sl, orc, variant, shape):
 
 
 # every variant at the widest row it holds (several row groups, column chunks beyond the first)
-@pytest.mark.parametrize("variant,F", [(2, 2048), (4, 2048), (5, 2048), (6, 2048), (6, 4096), (7, 2048), (7, 8192),
-                                       (8, 16384), (9, 8192), (11, 16384), (12, 8192), (13, 4096), (14, 8192),
+@pytest.mark.parametrize("variant,F", [(2, 2048), (4, 2048), (5, 2048), (6, 2048), (6, 4096),
+                                       (11, 16384), (12, 8192), (13, 4096), (14, 8192),
                                        (15, 4096), (16, 4096), (17, 2048), (18, 3072), (19, 1024), (20, 8192), (21, 8192),
                                        (22, 4096), (23, 5376), (24, 2048), (25, 2048), (26, 16384), (27, 1024), (28, 1024), (29, 2048)])
 def test_lr_variants_at_full_width(sl, orc, variant, F):
@@ -677,3 +677,19 @@ def test_stream_without_a_complete_row_keeps_the_sealed_shard(sl, orc):
         with pytest.raises(sl.SlError):
             r.shard_end()
         assert r.info("n_rows") == n
+
+
+@pytest.mark.parametrize("path,variant,F", [(1, 1, 1024), (1, 22, 4096), (6, 0, 1024)])
+def test_gradient_outside_the_fixed_point_range_is_reported(sl, orc, path, variant, F):
+    # features scaled by 1e7: the per-column gradient sums leave the 64-bit fixed-point range; the call must
+    # say so (SL_EINVAL) instead of returning a wrapped model with SL_OK
+    n, B = 8192, 4096
+    X, y = orc.synth(0, n, F)
+    X = (X * np.float32(1e7)).astype(np.float32)
+    with sl.Replica(F, B, eta=1e-12) as r:
+        r.set_option("path", path)
+        r.set_option("variant", variant)
+        r.load_shard(X, y)
+        with pytest.raises(sl.SlError) as ei:
+            r.train_steps(2)
+        assert ei.value.code == -1 and "range" in str(ei.value)

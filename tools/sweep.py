@@ -18,15 +18,9 @@ ap.add_argument("--grids", default="0")
 ap.add_argument("--paths", default="1")
 ap.add_argument("--ring", type=int, default=0)
 ap.add_argument("--krep", type=int, default=0)
-ap.add_argument("--direct", type=int, default=0)
-ap.add_argument("--hold", type=int, default=0)
-ap.add_argument("--rotate", type=int, default=0)
-ap.add_argument("--persist", type=int, default=0)
-ap.add_argument("--pause", type=int, default=0)
 ap.add_argument("--skip", type=int, default=0)
 ap.add_argument("--chunk", type=int, default=0)
 ap.add_argument("--loss", type=int, default=0)
-ap.add_argument("--relaxed", type=int, default=0)
 ap.add_argument("--block", type=int, default=0)
 a = ap.parse_args()
 peak = 6538.3
@@ -36,7 +30,7 @@ with Replica(a.F, a.B) as r:
     for path in [int(x) for x in a.paths.split(",")]:
         for v in [int(x) for x in a.variants.split(",")]:
             for g in [int(x) for x in a.grids.split(",")]:
-                r.set_option("ring_slots", a.ring); r.set_option("krep", a.krep); r.set_option("direct_total", a.direct); r.set_option("hold_refills", a.hold); r.set_option("rotate_reduce", a.rotate); r.set_option("persist_l2", a.persist); r.set_option("poll_pause", a.pause); r.set_option("relaxed_signal", a.relaxed); r.set_option("block_rows", a.block); r.set_option("debug_skip_compute", a.skip); r.set_option("tma_chunk", a.chunk); r.set_option("path", path); r.set_option("variant", v); r.set_option("grid", g)
+                r.set_option("ring_slots", a.ring); r.set_option("krep", a.krep); r.set_option("block_rows", a.block); r.set_option("debug_skip_compute", a.skip); r.set_option("tma_chunk", a.chunk); r.set_option("path", path); r.set_option("variant", v); r.set_option("grid", g)
                 try:
                     r.train_steps(64, want_loss=False)
                     best = 1e9
