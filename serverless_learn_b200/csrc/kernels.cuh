@@ -125,6 +125,12 @@ constexpr int kErrTimeoutW = 3;
 #endif
 constexpr int kErrTimeoutPeer = 4;
 constexpr int kErrRange = 5;   // a gradient partial left the fixed-point range (reported as SL_EINVAL, not as a timeout)
+// The error word lives in page-locked HOST memory (the host reads it after the launch): plain loads and stores
+// only — an atomic on it would be an atomic across PCIe, which this platform does not take from a whole grid.
+// First writer wins as far as the check can tell; a later code overwriting an earlier one is harmless.
+__device__ __forceinline__ void set_err(int* err, int code) {
+    if (ld_vol_s32(err) == 0) asm volatile("st.volatile.global.s32 [%0], %1;" ::"l"(err), "r"(code) : "memory");
+}
 __device__ __forceinline__ bool spin_abort(uint32_t& spins, int* err, int code,
                                            uint32_t limit = kSpinLimit) {
     ++spins;
@@ -132,7 +138,7 @@ __device__ __forceinline__ bool spin_abort(uint32_t& spins, int* err, int code,
     if ((spins & 1023u) == 0) {
         if (ld_vol_s32(err) != 0) return true;
         if (spins >= limit) {
-            atomicCAS(err, 0, code);
+            set_err(err, code);
             return true;
         }
     }
@@ -381,7 +387,7 @@ __device__ __forceinline__ long long to_fix(float v) { return __float2ll_rn(v * 
 // are added up; NaN too) is reported through the watchdog word instead of wrapping silently.
 __device__ __forceinline__ void check_fix_range(const float4& t, float limit, int* err) {
     const float m = fmaxf(fmaxf(fabsf(t.x), fabsf(t.y)), fmaxf(fabsf(t.z), fabsf(t.w)));
-    if (!(m < limit)) atomicCAS(err, 0, kErrRange);
+    if (!(m < limit)) set_err(err, kErrRange);
 }
 
 template <int CH, int R, int RS, int NCW, bool XB, int WM>

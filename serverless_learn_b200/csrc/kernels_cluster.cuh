@@ -457,7 +457,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             // into registers) until the partials have been read: the two would queue in the same pipe
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(xdone));
-            if (bad) atomicCAS(a.err, 0, kErrRange);
+            if (bad) set_err(a.err, kErrRange);
             if (t == 0) cl_stamp(a, s, 7);
             poll_totals<false, XC>(lp, lact, lpv, T, (unsigned)a.ncl, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPart, kSpinLimit);
 #pragma unroll

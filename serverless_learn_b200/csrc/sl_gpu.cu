@@ -250,7 +250,11 @@ struct sl_handle {
     int sym_n = 0;
     bool ipc_attached = false;
 
-    std::mutex mu;
+    std::mutex mu;       // replica state, shard, training stream: every entry point except the ingest ones below
+    std::mutex in_mu;    // the incoming stream (in_buf, in_len, staging ring, copy_stream): sl_shard_begin / append, and
+                         // sl_shard_end, which takes `mu` after it only for the swap — a ReceiveFile thread streams
+                         // while the training thread is inside a launch (src/worker.cc:242-246)
+    std::mutex err_mu;
     std::string err;
 };
 
@@ -271,8 +275,12 @@ int fail(sl_handle* h, int code, const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(buf, sizeof(buf), fmt, ap);
     va_end(ap);
-    if (h) h->err = buf;
-    else g_create_error = buf;
+    if (h) {
+        std::lock_guard<std::mutex> lk(h->err_mu);
+        h->err = buf;
+    } else {
+        g_create_error = buf;
+    }
     return code;
 }
 
@@ -1347,7 +1355,7 @@ long long sl_get_info(sl_handle* h, const char* key) {
 // ---- shard ingest -------------------------------------------------------------------
 int sl_shard_begin(sl_handle* h, size_t size_hint) {
     if (!h) return SL_EINVAL;
-    std::lock_guard<std::mutex> lk(h->mu);
+    std::lock_guard<std::mutex> lk(h->in_mu);
     DeviceGuard dg(h->device);
     // The sealed shard stays valid and trainable; the stream lands in a second buffer that
     // sl_shard_end swaps in (the reference receives files on a gRPC thread while the training
@@ -1364,7 +1372,7 @@ int sl_shard_begin(sl_handle* h, size_t size_hint) {
 
 int sl_shard_append(sl_handle* h, const void* bytes, size_t n) {
     if (!h) return SL_EINVAL;
-    std::lock_guard<std::mutex> lk(h->mu);
+    std::lock_guard<std::mutex> lk(h->in_mu);
     if (!h->shard_open) return fail(h, SL_ESTATE, "sl_shard_append without sl_shard_begin");
     if (n == 0) return SL_OK;
     if (!bytes) return fail(h, SL_EINVAL, "bytes is NULL");
@@ -1402,11 +1410,13 @@ int sl_shard_append(sl_handle* h, const void* bytes, size_t n) {
 
 int sl_shard_end(sl_handle* h, long long* n_rows) {
     if (!h) return SL_EINVAL;
-    std::lock_guard<std::mutex> lk(h->mu);
+    std::lock_guard<std::mutex> lk_in(h->in_mu);
     if (!h->shard_open) return fail(h, SL_ESTATE, "sl_shard_end without sl_shard_begin");
     DeviceGuard dg(h->device);
-    CK(h, cudaStreamSynchronize(h->copy_stream));
-    CK(h, cudaStreamSynchronize(h->stream));  // no kernel may still read the outgoing shard
+    CK(h, cudaStreamSynchronize(h->copy_stream));   // the stream has landed (the replica lock is not held while waiting)
+    // the swap itself: with the replica lock held no training call is in flight, so no kernel reads the outgoing shard
+    std::lock_guard<std::mutex> lk(h->mu);
+    CK(h, cudaStreamSynchronize(h->stream));
     // a self-describing stream is checked before it replaces the sealed shard
     size_t off = 0;
     unsigned long long row0 = 0;
@@ -1532,7 +1542,6 @@ int sl_shard_synth(sl_handle* h, long long n_rows, unsigned long long row0,
     h->shard_off = 0;
     h->shard_row0 = row0;
     h->n_rows = n_rows;
-    h->shard_open = false;
     h->shard_sealed = true;
     h->step = 0;
     return SL_OK;

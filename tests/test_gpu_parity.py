@@ -693,3 +693,43 @@ def test_gradient_outside_the_fixed_point_range_is_reported(sl, orc, path, varia
         with pytest.raises(sl.SlError) as ei:
             r.train_steps(2)
         assert ei.value.code == -1 and "range" in str(ei.value)
+
+
+def test_ingest_streams_while_a_training_call_is_in_flight(sl, orc):
+    # The reference receives files on a gRPC thread while the training thread runs (src/worker.cc:242-246):
+    # sl_shard_append must not wait for a training launch.  A trainer thread sits in one long call; a streamer
+    # thread pushes the next shard meanwhile and must be done appending long before the call returns.  Only
+    # sl_shard_end (the swap) waits for the call.
+    import threading
+    import time
+    n, F, B = 1 << 16, 1024, 4096
+    with sl.Replica(F, B, eta=0.0) as r:
+        r.shard_synth(n)
+        r.train_steps(64, want_loss=False)                        # warm
+        nxt = np.zeros(64 << 20, dtype=np.uint8)                  # 64 MiB of rows for the next shard
+        stamps = {}
+
+        def trainer():
+            stamps["train_start"] = time.perf_counter()
+            r.train_steps(300_000, want_loss=False)               # about a second on the device
+            stamps["train_done"] = time.perf_counter()
+
+        def streamer():
+            while "train_start" not in stamps:
+                time.sleep(0.0005)
+            time.sleep(0.02)                                      # the trainer is inside its call now
+            r.shard_begin(nxt.size)
+            for o in range(0, nxt.size, 1 << 20):
+                r.shard_append(nxt[o:o + (1 << 20)])
+            stamps["append_done"] = time.perf_counter()
+            r.shard_end()
+            stamps["end_done"] = time.perf_counter()
+
+        ts = [threading.Thread(target=trainer), threading.Thread(target=streamer)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        assert stamps["append_done"] < stamps["train_done"], stamps     # streamed during the launch
+        assert stamps["end_done"] >= stamps["train_done"]               # the swap waited for it
+        assert r.info("n_rows") == nxt.size // (4 * (F + 1)) and r.info("step") == 0
