@@ -127,9 +127,10 @@ constexpr int kErrTimeoutPeer = 4;
 constexpr int kErrRange = 5;   // a gradient partial left the fixed-point range (reported as SL_EINVAL, not as a timeout)
 // The error word lives in page-locked HOST memory (the host reads it after the launch): plain loads and stores
 // only — an atomic on it would be an atomic across PCIe, which this platform does not take from a whole grid.
-// First writer wins as far as the check can tell; a later code overwriting an earlier one is harmless.
+// A posted store, no read-back (thousands of threads may report at once; reads of host memory would queue up on
+// PCIe): a later code overwriting an earlier one is harmless, any non-zero value fails the call.
 __device__ __forceinline__ void set_err(int* err, int code) {
-    if (ld_vol_s32(err) == 0) asm volatile("st.volatile.global.s32 [%0], %1;" ::"l"(err), "r"(code) : "memory");
+    asm volatile("st.volatile.global.s32 [%0], %1;" ::"l"(err), "r"(code) : "memory");
 }
 __device__ __forceinline__ bool spin_abort(uint32_t& spins, int* err, int code,
                                            uint32_t limit = kSpinLimit) {
@@ -385,9 +386,12 @@ __device__ __forceinline__ void red_add_u64(unsigned long long* p, unsigned long
 __device__ __forceinline__ long long to_fix(float v) { return __float2ll_rn(v * 68719476736.0f); }
 // Sums of these integers must fit 64 bits: a partial beyond `limit` (2^27 over the number of partials that
 // are added up; NaN too) is reported through the watchdog word instead of wrapping silently.
-__device__ __forceinline__ void check_fix_range(const float4& t, float limit, int* err) {
+__device__ __forceinline__ bool fix_out_of_range(const float4& t, float limit) {
     const float m = fmaxf(fmaxf(fabsf(t.x), fabsf(t.y)), fmaxf(fabsf(t.z), fabsf(t.w)));
-    if (!(m < limit)) set_err(err, kErrRange);
+    return !(m < limit);
+}
+__device__ __forceinline__ void check_fix_range(const float4& t, float limit, int* err) {
+    if (fix_out_of_range(t, limit)) set_err(err, kErrRange);
 }
 
 template <int CH, int R, int RS, int NCW, bool XB, int WM>

@@ -307,6 +307,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                 // each partial goes to fixed point on its own, the sum is an integer sum: the same
                 // bits in any order (and the same bits as summing s64 partials would give)
                 long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+                bool bad = false;   // a partial outside the fixed-point range: reported once, after the loop
                 const float* src = part + oe;
                 int pp = ogrp;
                 for (; pp + 3 * ngrp < P; pp += 4 * ngrp) {
@@ -314,10 +315,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                     const float4 v1 = ld_vol_f32x4(src + (size_t)(pp + ngrp) * a.Fp);
                     const float4 v2 = ld_vol_f32x4(src + (size_t)(pp + 2 * ngrp) * a.Fp);
                     const float4 v3 = ld_vol_f32x4(src + (size_t)(pp + 3 * ngrp) * a.Fp);
-                    check_fix_range(v0, a.fix_limit, a.err);
-                    check_fix_range(v1, a.fix_limit, a.err);
-                    check_fix_range(v2, a.fix_limit, a.err);
-                    check_fix_range(v3, a.fix_limit, a.err);
+                    bad = bad || fix_out_of_range(v0, a.fix_limit) || fix_out_of_range(v1, a.fix_limit) ||
+                          fix_out_of_range(v2, a.fix_limit) || fix_out_of_range(v3, a.fix_limit);
                     t0 += (to_fix(v0.x) + to_fix(v1.x)) + (to_fix(v2.x) + to_fix(v3.x));
                     t1 += (to_fix(v0.y) + to_fix(v1.y)) + (to_fix(v2.y) + to_fix(v3.y));
                     t2 += (to_fix(v0.z) + to_fix(v1.z)) + (to_fix(v2.z) + to_fix(v3.z));
@@ -325,9 +324,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) lr_wide_kernel(const LrArgs
                 }
                 for (; pp < P; pp += ngrp) {
                     const float4 v0 = ld_vol_f32x4(src + (size_t)pp * a.Fp);
-                    check_fix_range(v0, a.fix_limit, a.err);
+                    bad = bad || fix_out_of_range(v0, a.fix_limit);
                     t0 += to_fix(v0.x); t1 += to_fix(v0.y); t2 += to_fix(v0.z); t3 += to_fix(v0.w);
                 }
+                if (bad) set_err(a.err, kErrRange);
                 longlong2* dst = reinterpret_cast<longlong2*>(gsm + (size_t)ogrp * L + 4 * oj);
                 dst[0] = make_longlong2(t0, t1);
                 dst[1] = make_longlong2(t2, t3);
