@@ -1218,6 +1218,10 @@ int sl_create(int device, int D, int F, int B, double eta, double lambda, sl_han
     if (!h) return fail(nullptr, SL_ENOMEM, "out of host memory");
     h->device = device;
     h->D = D; h->F = F; h->B = B; h->eta = eta; h->lambda = lambda;
+    // profilers replay kernels one at a time and do not take every launch form: SL_CL_COOP=0 / SL_CL_GRAPH=0 make
+    // the cluster kernel launch without the cooperative attribute / outside a graph (same kernel, same arguments)
+    if (const char* e = getenv("SL_CL_COOP")) h->cl_coop = atoi(e) ? -1 : 0;
+    if (const char* e = getenv("SL_CL_GRAPH")) h->opt_cl_graph = atoi(e);
     DeviceGuard dg(device);
 #define CKC(call)                                                                          \
     do {                                                                                   \
