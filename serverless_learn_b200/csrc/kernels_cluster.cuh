@@ -110,9 +110,24 @@ __device__ __forceinline__ void st_async_b32(uint32_t raddr, uint32_t v, uint32_
                  "r"(rbar)
                  : "memory");
 }
-// wait on a barrier whose bytes were written by other CTAs of the cluster
+// Wait on a barrier whose bytes were written by other CTAs of the cluster (st.async: the bytes are counted
+// on the barrier as they land in THIS CTA's shared memory).  The wait is the plain CTA-scope one: a cluster-scope
+// acquire compiles to an L1 invalidation (CCTL.IVALL) in EVERY turn of the spin loop — a quarter of all stall
+// samples of the kernel in the first profile — and there is nothing in L1 to invalidate: the data is in shared memory.
+#ifndef SL_CL_POLL_ACQ
+#define SL_CL_POLL_ACQ 0
+#endif
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+#ifndef SL_CL_WAIT_MODE
+#define SL_CL_WAIT_MODE 0   // 0: try_wait.acquire.cluster, 1: test_wait (pure polling, CTA scope)
+#endif
 __device__ __forceinline__ uint32_t mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
     uint32_t ok;
+#if SL_CL_WAIT_MODE == 0
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
@@ -120,6 +135,15 @@ __device__ __forceinline__ uint32_t mbar_try_wait_cluster(uint32_t bar, uint32_t
         : "=r"(ok)
         : "r"(bar), "r"(parity)
         : "memory");
+#else
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+#endif
     return ok;
 }
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* err) {
@@ -127,9 +151,6 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
     while (!mbar_try_wait_cluster(bar, parity)) {
         if (spin_abort(spins, err, kErrTimeoutMbar)) return;
     }
-}
-__device__ __forceinline__ void red_add_u64_sys(unsigned long long* p, unsigned long long v) {
-    asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
     asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -212,7 +233,7 @@ __device__ __forceinline__ void poll_totals(unsigned long long* const (&p)[XC], 
         unsigned long long v[XC];
 #pragma unroll
         for (int i = 0; i < XC; ++i)
-            if (!done[i]) v[i] = SYS ? ld_relaxed_sys_u64(p[i]) : ld_relaxed_u64(p[i]);
+            if (!done[i]) v[i] = SYS ? ld_relaxed_sys_u64(p[i]) : (SL_CL_POLL_ACQ ? ld_acquire_u64(p[i]) : ld_relaxed_u64(p[i]));
         bool all = true;
 #pragma unroll
         for (int i = 0; i < XC; ++i) {
