@@ -678,18 +678,10 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
         if (!fits(kClVariants[vi])) { *why = "requested cluster variant does not hold this F"; return false; }
     } else {
         // measured at config 3 (tools/k1c_bench.py, profiles/r2_k1c.md): clusters of 4 put 132 of the 148 SMs to
-        // work (clusters of 8 only tile 120); with at most 32 rows per CTA and step the whole step is one pass of
-        // two 16-row groups and the row copies are issued by an exchange warp (15), otherwise by their own warp (5)
-        if (F <= 512) {
-            vi = 3;
-        } else {
-            const long long beff = (long long)h->B * (h->vw > 1 ? h->vw : 1);
-            int ncl5 = cluster_capacity(h, 4);
-            if (h->opt_clusters > 0) ncl5 = (int)std::min<long long>(ncl5, h->opt_clusters);
-            else if (h->opt_grid > 0) ncl5 = (int)std::max<long long>(1, std::min<long long>(ncl5, h->opt_grid / 4));
-            const long long rows_cta = ncl5 > 0 ? (beff + 4LL * ncl5 - 1) / (4LL * ncl5) : 1 << 30;
-            vi = rows_cta <= 32 ? 14 : 4;
-        }
+        // work (clusters of 8 only tile 120), and 16 compute warps take a CTA's 32 rows of a step in one pass.
+        // Variant 15 (row copies issued by an exchange warp, 20 warps) measures within a few percent of 5 either
+        // way from box to box; 5 also serves shapes with several passes per step.
+        vi = F <= 512 ? 3 : 4;
         if (!fits(kClVariants[vi]) || cluster_capacity(h, vi) < 1) {
             vi = -1;
             for (int k = 0; k < kNumClVariants; ++k)
