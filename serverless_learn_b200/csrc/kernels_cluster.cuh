@@ -60,6 +60,7 @@ struct ClArgs {
     float part_limit;      // |partial| above this could overflow the accumulator word
     int poll_delay, poll_gap;  // SM cycles before the first look at an accumulator / between looks
     int xpoll_delay, xpoll_gap;  // the same for the all-rank words
+    int wait_all_owners;   // diagnostics: 1 = a compute thread waits for every owner's weights, not only its columns' owner
     int* err;              // 0 = ok; set by the watchdog
     // geometry, computed on the host
     int ncl;               // clusters in the grid
@@ -285,8 +286,8 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.off_bar);      // [RG*nsg]
     uint64_t* empty = full + RG * nsg;                                   // [RG*nsg]
     uint64_t* rfull = empty + RG * nsg;                                  // gradient partials of a step landed
-    uint64_t* wfull = rfull + 1;                                         // next step's weights landed
-    uint64_t* lfull = wfull + 1;                                         // [2] loss partials of a step landed
+    uint64_t* wfull = rfull + 1;                                         // [CS] next step's weights of owner o landed
+    uint64_t* lfull = wfull + CS;                                        // [2] loss partials of a step landed
     uint64_t* xdone = lfull + 2;                                         // the exchange warps have read this step's partials
     float* recv = reinterpret_cast<float*>(smem + a.off_recv);          // [NSRC][fc]
     float* wsm = reinterpret_cast<float*>(smem + a.off_wsm);            // [2][F]
@@ -319,14 +320,15 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             mbar_init(smem_u32(&empty[s]), WPG);
         }
         mbar_init(smem_u32(rfull), 1);
-        mbar_init(smem_u32(wfull), 1);
+        for (int o = 0; o < CS; ++o) mbar_init(smem_u32(&wfull[o]), 1);
         mbar_init(smem_u32(&lfull[0]), 1);
         mbar_init(smem_u32(&lfull[1]), 1);
         mbar_init(smem_u32(xdone), XW);
         fence_mbar_init();
         // what the first phases will receive (later phases are armed by their waiters)
         if (n_steps > 0) mbar_arrive_expect_tx(smem_u32(rfull), recv_bytes);
-        if (n_steps > 1) mbar_arrive_expect_tx(smem_u32(wfull), (uint32_t)F * 4u);
+        if (n_steps > 1)
+            for (int o = 0; o < CS; ++o) mbar_arrive_expect_tx(smem_u32(&wfull[o]), (uint32_t)fc * 4u);
         if (want_loss && crank == 0) {
             if (n_steps > 0) mbar_arrive_expect_tx(smem_u32(&lfull[0]), (uint32_t)NSRC * 4u);
             if (n_steps > 1) mbar_arrive_expect_tx(smem_u32(&lfull[1]), (uint32_t)NSRC * 4u);
@@ -571,7 +573,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
 #pragma unroll
                     for (int d0 = 0; d0 < CS; d0 += 4) {
                         const int d = d0 + (lane & 3);
-                        if (d < CS) st_async_v4(mapa_u32(dsta, (uint32_t)d), w4, mapa_u32(wfull_a, (uint32_t)d));
+                        if (d < CS) st_async_v4(mapa_u32(dsta, (uint32_t)d), w4, mapa_u32(wfull_a + 8u * crank, (uint32_t)d));
                     }
                 }
             }
@@ -647,8 +649,16 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             float2* zyb = zy + (size_t)(s & 1) * a.zy_rows;
             if (tid == 0) cl_stamp(a, s, 0);
             auto take_weights = [&]() {
-                mbar_wait_cluster(smem_u32(wfull), (uint32_t)(s - 1) & 1u, a.err);
-                if (tid == 0 && s + 1 < n_steps) mbar_arrive_expect_tx(smem_u32(wfull), (uint32_t)F * 4u);
+                // one barrier per owner CTA: a warp starts on its columns as soon as THEIR owner's weights are here
+                // (the owners finish their L2 hop up to half a microsecond apart); the thread that holds an owner's
+                // first columns re-arms that barrier
+                if (gv) {
+                    if (a.wait_all_owners)   // comparison switch: behave as one barrier for all weights
+                        for (int o = 0; o < CS; ++o) mbar_wait_cluster(smem_u32(&wfull[o]), (uint32_t)(s - 1) & 1u, a.err);
+                    mbar_wait_cluster(smem_u32(&wfull[owner]), (uint32_t)(s - 1) & 1u, a.err);
+                    if (rg == 0 && gq * 4 == owner * fc && s + 1 < n_steps)
+                        mbar_arrive_expect_tx(smem_u32(&wfull[owner]), (uint32_t)fc * 4u);
+                }
                 if (gv) w = lds_v4(wsm_a + (uint32_t)((s & 1) * F + gq * 4) * 4u);
             };
             if (nsb == 0 && s > 0) take_weights();  // a CTA without rows still takes part in every exchange

@@ -243,7 +243,7 @@ struct sl_handle {
     int cl_graph_ok = -1;                // -1 not tried, 0 unusable here, 1 in use
     int cl_graph_variant = -1, cl_graph_grid = 0, cl_graph_threads = 0;
     size_t cl_graph_smem = 0;
-    long long opt_cl_variant = 0, opt_clusters = 0, opt_poll_delay = -1, opt_poll_gap = -1, opt_xpoll_delay = -1, opt_xpoll_gap = -1, opt_cl_graph = 1;
+    long long opt_cl_variant = 0, opt_clusters = 0, opt_poll_delay = -1, opt_poll_gap = -1, opt_xpoll_delay = -1, opt_xpoll_gap = -1, opt_cl_graph = 1, opt_wait_all = 0;
     // caller-provided symmetric allocation for K1c's all-rank words (sl_peer_attach_symmetric)
     unsigned long long* sym_buf[8] = {};
     unsigned long long* mc_gx = nullptr; // its multicast alias (one store reaches every rank), or nullptr
@@ -717,14 +717,14 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     const size_t yb_b = sizeof(float) * 2 * (size_t)v.rg * a.ycap;
     const size_t slot_b = (size_t)v.rs * a.row_bytes;
     const size_t prev_b = 8 * (2 * (size_t)a.fc + 4);  // + the loss accumulators' values
-    const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + yb_b + prev_b + 8 * (2 * 32 + 6) + 512;
+    const size_t fixed = recv_b + wsm_b + lrecv_b + red_b + zy_b + yb_b + prev_b + 8 * (2 * 32 + 6 + 16) + 512;
     if (h->smem_optin < fixed + (size_t)v.rg * slot_b) { *why = "the ring does not fit in shared memory"; return false; }
     size_t nsg = (h->smem_optin - fixed) / ((size_t)v.rg * slot_b);
     nsg = std::min<size_t>(nsg, (size_t)(32 / v.rg));  // one producer lane per slot
     if (h->opt_ring > 0) nsg = std::max<size_t>(1, std::min<size_t>(nsg, (size_t)h->opt_ring));
     a.nsg = (int)nsg;
     size_t off = (size_t)v.rg * nsg * slot_b;
-    off = align_up(off, 16); a.off_bar = (int)off;    off += 8 * (2 * (size_t)v.rg * nsg + 6);
+    off = align_up(off, 16); a.off_bar = (int)off;    off += 8 * (2 * (size_t)v.rg * nsg + 6 + (size_t)v.cs);
     off = align_up(off, 16); a.off_recv = (int)off;   off += recv_b;
     off = align_up(off, 16); a.off_wsm = (int)off;    off += wsm_b;
     off = align_up(off, 16); a.off_lrecv = (int)off;  off += lrecv_b;
@@ -741,6 +741,7 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     a.poll_gap = h->opt_poll_gap >= 0 ? (int)h->opt_poll_gap : 0;
     a.xpoll_delay = h->opt_xpoll_delay >= 0 ? (int)h->opt_xpoll_delay : 0;
     a.xpoll_gap = h->opt_xpoll_gap >= 0 ? (int)h->opt_xpoll_gap : 0;
+    a.wait_all_owners = h->opt_wait_all != 0 ? 1 : 0;
     p->smem = off;
     p->variant = vi;
     p->grid = grid;
@@ -1318,6 +1319,7 @@ int sl_set_option(sl_handle* h, const char* key, long long value) {
     else if (k == "xpoll_delay") h->opt_xpoll_delay = value;
     else if (k == "xpoll_gap") h->opt_xpoll_gap = value;
     else if (k == "cl_graph") h->opt_cl_graph = value;
+    else if (k == "wait_all_owners") h->opt_wait_all = value;
     else if (k == "cl_coop") h->cl_coop = value < 0 ? -1 : (value ? 1 : 0);
     else return fail(h, SL_EINVAL, "unknown option '%s'", key);
     return SL_OK;

@@ -25,6 +25,7 @@ ap.add_argument("--path", type=int, default=6)
 ap.add_argument("--delay", default="-1")
 ap.add_argument("--coop", type=int, default=-1)
 ap.add_argument("--graph", type=int, default=1)
+ap.add_argument("--waitall", default="0")
 ap.add_argument("--fused1", action="store_true", help="attach this replica to itself (1 rank): the cross-GPU stage runs against the own memory")
 ap.add_argument("--gap", default="-1")
 ap.add_argument("--timeline", action="store_true")
@@ -50,7 +51,9 @@ with Replica(a.F, a.B) as r:
           for delay in [int(x) for x in a.delay.split(",")]:
            for gap in [int(x) for x in a.gap.split(",")]:
             r.set_option("poll_delay", delay); r.set_option("poll_gap", gap)
-            for steps in [int(x) for x in a.steps.split(",")]:
+
+            for steps, wa in [(int(x), int(w)) for x in a.steps.split(",") for w in a.waitall.split(",")]:
+                r.set_option("wait_all_owners", wa)
                 r.set_option("cl_variant", clv); r.set_option("clusters", ncl); r.set_option("ring_slots", a.ring)
                 r.set_option("debug_timeline", -1)
                 try:
@@ -60,7 +63,7 @@ with Replica(a.F, a.B) as r:
                         r.train_steps(steps, want_loss=bool(a.loss))
                         ts.append(r.last_train_ms())
                     us = float(np.median(ts)) * 1e3 / steps
-                    print(f"clv={clv} delay={delay} gap={gap} grid={r.info('grid')} slots={r.info('ring_slots')} steps={steps} "
+                    print(f"clv={clv} waitall={wa} delay={delay} gap={gap} grid={r.info('grid')} slots={r.info('ring_slots')} steps={steps} "
                           f"{us:8.3f} us/step (min {min(ts) * 1e3 / steps:.3f})  {algo / us / 1e3:8.1f} GB/s  "
                           f"frac={algo / us / 1e3 / peak:.3f}", flush=True)
                 except SlError as e:
