@@ -169,6 +169,27 @@ int sl_set_state(sl_handle* h, const double* model, const double* old, int n);
  * reads and writes the initiator's state through peer-mapped memory (NVLink) — no host staging,
  * no wire.  Bit-exact with sl_delta_snapshot -> sl_merge -> sl_apply_reply. */
 int sl_gossip_p2p(sl_handle* initiator, sl_handle* callee);
+/* The same one-kernel round between worker PROCESSES on one box — the reference's deployment, one worker per
+ * process (src/worker.cc:233-258), where today the round is three blocking calls through host buffers.
+ *   once:   initiator  sl_state_export(h, handles128)        two 64-byte IPC handles (model, old)
+ *           callee     sl_state_attach(h, handles128, n, initiator's lambda, &peer)   maps them (<= 16 peers)
+ *   round:  initiator  sl_state_lend(h)      waits for its own work, then keeps every other call on h out
+ *           initiator -> callee: any doorbell (an ExchangeUpdates request with an empty delta will do)
+ *           callee     sl_gossip_p2p_remote(h, peer)   src/worker.cc:194-219 + :81-100 in one kernel on the
+ *                      callee's GPU, the initiator's state read and written through the mapping (NVLink, or
+ *                      the same GPU's memory); returns when the kernel has finished
+ *           callee -> initiator: the (empty) reply
+ *           initiator  sl_state_reclaim(h)   same thread as sl_state_lend
+ * Bit-exact with sl_delta_snapshot -> sl_merge -> sl_apply_reply and with sl_gossip_p2p.  The handles are those
+ * of cudaMalloc allocations: both processes need the same box and CUDA IPC (not available inside one process —
+ * use sl_gossip_p2p there).  sl_state_detach unmaps a peer that has left (the initiator must outlive the
+ * mapping's last use, as with any IPC memory). */
+int sl_state_export(sl_handle* h, void* handles128);
+int sl_state_attach(sl_handle* h, const void* handles128, int n, double peer_lambda, int* peer_out);
+int sl_state_detach(sl_handle* h, int peer);
+int sl_state_lend(sl_handle* h);
+int sl_state_reclaim(sl_handle* h);
+int sl_gossip_p2p_remote(sl_handle* callee, int peer);
 
 /* Fused path (preferred): sl_peer_export yields a 64-byte IPC handle of this replica's inbox;
  * gather the handles of all ranks (rank order) and pass them to sl_peer_attach on every rank

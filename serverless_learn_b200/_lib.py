@@ -37,6 +37,12 @@ _SIGS = {
     "sl_get_old": (C.c_int, [_h, _dp, C.c_int]),
     "sl_set_state": (C.c_int, [_h, _dp, _dp, C.c_int]),
     "sl_gossip_p2p": (C.c_int, [_h, _h]),
+    "sl_state_export": (C.c_int, [_h, C.c_void_p]),
+    "sl_state_attach": (C.c_int, [_h, C.c_void_p, C.c_int, C.c_double, C.POINTER(C.c_int)]),
+    "sl_state_detach": (C.c_int, [_h, C.c_int]),
+    "sl_state_lend": (C.c_int, [_h]),
+    "sl_state_reclaim": (C.c_int, [_h]),
+    "sl_gossip_p2p_remote": (C.c_int, [_h, C.c_int]),
     "sl_peer_export": (C.c_int, [_h, C.c_void_p]),
     "sl_peer_attach": (C.c_int, [_h, C.c_int, C.c_int, C.c_void_p]),
     "sl_peer_attach_symmetric": (C.c_int, [_h, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.c_void_p, C.c_size_t]),

@@ -216,6 +216,30 @@ class Replica:
         """One gossip round with `callee` (this replica initiates), entirely on the GPUs."""
         self._ck(self._L.sl_gossip_p2p(self._h, callee._h))
 
+    # -- the same round between worker processes (include/sl_gpu.h: sl_state_*) --
+    def state_export(self) -> bytes:
+        buf = C.create_string_buffer(128)
+        self._ck(self._L.sl_state_export(self._h, buf))
+        return buf.raw
+
+    def state_attach(self, handles: bytes, n: int, peer_lambda: float) -> int:
+        peer = C.c_int(-1)
+        self._ck(self._L.sl_state_attach(self._h, C.create_string_buffer(handles, 128), n, peer_lambda, C.byref(peer)))
+        return peer.value
+
+    def state_detach(self, peer: int) -> None:
+        self._ck(self._L.sl_state_detach(self._h, peer))
+
+    def state_lend(self) -> None:
+        self._ck(self._L.sl_state_lend(self._h))
+
+    def state_reclaim(self) -> None:
+        self._ck(self._L.sl_state_reclaim(self._h))
+
+    def gossip_p2p_remote(self, peer: int) -> None:
+        """One gossip round initiated by the worker process whose state is attached as `peer`; runs here."""
+        self._ck(self._L.sl_gossip_p2p_remote(self._h, peer))
+
     def peer_export(self) -> bytes:
         buf = C.create_string_buffer(64)
         self._ck(self._L.sl_peer_export(self._h, buf))

@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -154,6 +155,7 @@ constexpr int kNumClVariants = sizeof(kClVariants) / sizeof(kClVariants[0]);
 
 }  // namespace
 
+constexpr int kMaxRemoteStates = 16;
 struct sl_handle {
     int device = 0;
     int D = 0, F = 0, B = 0;
@@ -226,6 +228,11 @@ struct sl_handle {
     void* peer_base[8] = {nullptr};      // xblock of every rank as mapped here (own = xblock)
     int peer_n = 0, peer_rank = 0;       // 0 = not attached
     unsigned xflag_base = 0;
+    // states of workers in OTHER processes, mapped here for the one-kernel gossip round (sl_state_attach)
+    struct RemoteState { double* model = nullptr; double* old = nullptr; double lambda = 0; bool used = false; };
+    RemoteState remote[kMaxRemoteStates];
+    std::thread::id lent_by;             // thread that holds mu between sl_state_lend and sl_state_reclaim
+    bool lent = false;
     long long opt_sync_path = 0;         // 0 auto (fused when attached), 1 NCCL per step
     // cluster kernel (K1c)
     unsigned long long* cl_scratch = nullptr;  // [gacc 2F][gbase 2F][lacc 3 + pad][lbase 3 + pad]
@@ -1273,6 +1280,8 @@ int sl_destroy(sl_handle* h) {
     if (h->cl_graph) cudaGraphDestroy(h->cl_graph);
     for (int p = 0; p < h->peer_n; ++p)
         if (p != h->peer_rank && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
+    for (auto& r : h->remote)
+        if (r.used) { cudaIpcCloseMemHandle(r.model); cudaIpcCloseMemHandle(r.old); }
     cudaFree(h->xblock);
     cudaFree(h->resid); cudaFree(h->rowloss); cudaFree(h->gpart); cudaFree(h->gsum);
     if (h->h_in) cudaFreeHost(h->h_in);
@@ -1809,6 +1818,104 @@ int sl_gossip_p2p(sl_handle* initiator, sl_handle* callee) {
     const int n = callee->D;
     slk::gossip_p2p_kernel<<<(n + 127) / 128, 128, 0, callee->stream>>>(
         initiator->model, initiator->old, callee->model, callee->old, n, initiator->lambda, callee->lambda);
+    callee->launches++;
+    CK(callee, cudaGetLastError());
+    CK(callee, cudaStreamSynchronize(callee->stream));
+    return SL_OK;
+}
+
+// ---- the same round between worker PROCESSES (the reference's deployment: one worker per process,
+// src/worker.cc:233-258).  The initiator's model / old are plain cudaMalloc allocations: their IPC handles
+// travel once (any channel), the callee maps them and from then on runs the round as one kernel on its own GPU.
+int sl_state_export(sl_handle* h, void* handles128) {
+    if (!h || !handles128) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);
+    cudaIpcMemHandle_t ih[2];
+    CK(h, cudaIpcGetMemHandle(&ih[0], h->model));
+    CK(h, cudaIpcGetMemHandle(&ih[1], h->old));
+    memcpy(handles128, ih, sizeof(ih));
+    return SL_OK;
+}
+
+int sl_state_attach(sl_handle* h, const void* handles128, int n, double peer_lambda, int* peer_out) {
+    if (!h || !handles128 || !peer_out) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (n != h->D) return fail(h, SL_EINVAL, "sl_state_attach: model lengths differ (%d vs %d)", n, h->D);
+    int slot = -1;
+    for (int i = 0; i < kMaxRemoteStates; ++i)
+        if (!h->remote[i].used) { slot = i; break; }
+    if (slot < 0) return fail(h, SL_ESTATE, "sl_state_attach: %d peer states are already attached", kMaxRemoteStates);
+    DeviceGuard dg(h->device);
+    cudaIpcMemHandle_t ih[2];
+    memcpy(ih, handles128, sizeof(ih));
+    void* ptr[2] = {nullptr, nullptr};
+    for (int k = 0; k < 2; ++k) {
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr[k], ih[k], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            if (k == 1) cudaIpcCloseMemHandle(ptr[0]);
+            return fail(h, SL_ECUDA, "cudaIpcOpenMemHandle(%s) failed: %s (same process, or no peer access?)",
+                        k ? "old" : "model", cudaGetErrorString(e));
+        }
+    }
+    h->remote[slot].model = static_cast<double*>(ptr[0]);
+    h->remote[slot].old = static_cast<double*>(ptr[1]);
+    h->remote[slot].lambda = peer_lambda;
+    h->remote[slot].used = true;
+    *peer_out = slot;
+    return SL_OK;
+}
+
+int sl_state_detach(sl_handle* h, int peer) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (peer < 0 || peer >= kMaxRemoteStates || !h->remote[peer].used)
+        return fail(h, SL_EINVAL, "sl_state_detach: no such peer state");
+    DeviceGuard dg(h->device);
+    CK(h, cudaStreamSynchronize(h->stream));
+    cudaIpcCloseMemHandle(h->remote[peer].model);
+    cudaIpcCloseMemHandle(h->remote[peer].old);
+    h->remote[peer] = sl_handle::RemoteState();
+    return SL_OK;
+}
+
+// Initiator side: nothing of this replica runs or starts between lend and reclaim (the peer's kernel owns the
+// state meanwhile).  The mutex is held across the two calls, so they come from one thread.
+int sl_state_lend(sl_handle* h) {
+    if (!h) return SL_EINVAL;
+    h->mu.lock();
+    DeviceGuard dg(h->device);
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) {
+        fail(h, SL_ECUDA, "sl_state_lend: %s", cudaGetErrorString(e));
+        h->mu.unlock();
+        return SL_ECUDA;
+    }
+    h->lent = true;
+    h->lent_by = std::this_thread::get_id();
+    return SL_OK;
+}
+
+int sl_state_reclaim(sl_handle* h) {
+    if (!h) return SL_EINVAL;
+    // only the lending thread can get here with lent == true and be the owner of mu
+    if (!h->lent || h->lent_by != std::this_thread::get_id()) return SL_ESTATE;
+    h->lent = false;
+    h->mu.unlock();
+    return SL_OK;
+}
+
+int sl_gossip_p2p_remote(sl_handle* callee, int peer) {
+    if (!callee) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(callee->mu);
+    if (peer < 0 || peer >= kMaxRemoteStates || !callee->remote[peer].used)
+        return fail(callee, SL_EINVAL, "sl_gossip_p2p_remote: no such peer state");
+    DeviceGuard dg(callee->device);
+    const sl_handle::RemoteState& r = callee->remote[peer];
+    const int n = callee->D;
+    slk::gossip_p2p_kernel<<<(n + 127) / 128, 128, 0, callee->stream>>>(r.model, r.old, callee->model, callee->old, n,
+                                                                       r.lambda, callee->lambda);
     callee->launches++;
     CK(callee, cudaGetLastError());
     CK(callee, cudaStreamSynchronize(callee->stream));

@@ -399,6 +399,79 @@ def test_gossip_p2p_bit_exact(sl, orc, n):
             A.gossip_p2p(A)
 
 
+@pytest.mark.parametrize("n", [7, 16384])
+def test_gossip_across_processes(sl, orc, n):
+    # The reference's deployment: one worker per process.  The initiator lives in a child process (on a second
+    # GPU when the box has one), this process is the callee: its kernel reads and writes the child's state through
+    # the IPC mapping.  Same bits as the three host-buffer calls and as the oracle.
+    import subprocess
+    import sys
+    import time
+    import torch
+    dev_a = 1 if torch.cuda.device_count() > 1 else 0
+    peer_py = os.path.join(os.path.dirname(os.path.abspath(__file__)), "xproc_gossip_peer.py")
+    child = subprocess.Popen([sys.executable, peer_py, str(n), str(dev_a), str(n)], stdin=subprocess.PIPE,
+                             stdout=subprocess.PIPE, text=True, bufsize=1)
+
+    def ask(msg=None):
+        if msg:
+            child.stdin.write(msg + "\n")
+            child.stdin.flush()
+        line = child.stdout.readline()
+        assert line, "the initiator process died"
+        return line.split()
+
+    try:
+        rng = np.random.default_rng(n)     # the child draws the same am, ao from the same seed
+        am, ao = (rng.standard_normal(n) * 10.0 ** rng.integers(-6, 6, n) for _ in range(2))
+        rng_b = np.random.default_rng(n + 1)
+        bm, bo = (rng_b.standard_normal(n) * 10.0 ** rng_b.integers(-6, 6, n) for _ in range(2))
+        tag, hexh = ask()
+        assert tag == "HANDLES"
+        with sl.Replica(n, 1, device=0, lam=0.25) as Bn:
+            Bn.set_state(bm, bo)
+            with pytest.raises(sl.SlError):
+                Bn.state_attach(bytes.fromhex(hexh), n + 1, 0.5)        # model lengths differ
+            with pytest.raises(sl.SlError):
+                Bn.gossip_p2p_remote(0)                                  # nothing attached yet
+            peer = Bn.state_attach(bytes.fromhex(hexh), n, 0.5)
+            for rnd in range(3):
+                with_tick = rnd == 1
+                assert ask("ROUND tick" if with_tick else "ROUND") == ["LENT"]
+                reps = 21 if rnd == 2 else 1      # the state stays lent: several rounds in a row are legal
+                for k in range(reps):
+                    if k == 1:
+                        t0 = time.perf_counter()
+                    Bn.gossip_p2p_remote(peer)
+                if reps > 1:
+                    dt = (time.perf_counter() - t0) / (reps - 1)
+                for k in range(reps):
+                    d = orc.delta(am, ao)
+                    rep = orc.merge_callee(bm, bo, d, 0.25)
+                    orc.apply_reply(am, ao, rep, 0.5)
+                reply = ask("DONE")
+                if with_tick:
+                    assert reply == ["TICK", "blocked"]      # the child's training thread waited for the round
+                    reply = ask()
+                    orc.train_tick(am)                         # src/worker.cc:226, after the round
+                assert reply[0] == "STATE"
+                cm = np.frombuffer(bytes.fromhex(reply[1]), dtype=np.float64)
+                co = np.frombuffer(bytes.fromhex(reply[2]), dtype=np.float64)
+                assert np.array_equal(cm, am) and np.array_equal(co, ao)
+                assert np.array_equal(Bn.model(), bm) and np.array_equal(Bn.old(), bo)
+            print(f"cross-process gossip round, n={n}, initiator on GPU {dev_a}: {dt * 1e6:.1f} us per round "
+                  "(call + kernel + sync)")
+            Bn.state_detach(peer)
+            with pytest.raises(sl.SlError):
+                Bn.gossip_p2p_remote(peer)
+        child.stdin.write("QUIT\n")
+        child.stdin.flush()
+        assert child.wait(timeout=60) == 0
+    finally:
+        if child.poll() is None:
+            child.kill()
+
+
 def test_launch_splitting_and_step_reset(sl, orc):
     n, F, B, steps, eta = 500, 128, 48, 10, 0.2
     X, y = orc.synth(0, n, F)
