@@ -56,6 +56,8 @@ class Update {
   public:
     int delta_size() const;
     double delta(int i) const;
+    void set_delta(int i, double v);
+    void add_delta(double v);
     const google::protobuf::RepeatedField<double>& delta() const;
     google::protobuf::RepeatedField<double>* mutable_delta();
     void clear_delta();
