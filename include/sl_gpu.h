@@ -213,6 +213,14 @@ int sl_peer_attach(sl_handle* h, int nranks, int rank, const void* handles);
  * them.  No reference counterpart. */
 int sl_peer_attach_symmetric(sl_handle* h, int nranks, int rank, const void* const* bufs, void* multicast,
                              size_t bytes);
+/* A worker joins or leaves the synchronous group (the membership changes of src/master.cc:79-91 and :177-196
+ * applied to this build-defined mode): EVERY member calls sl_peer_detach between two training calls, the callers
+ * meet (any barrier), then the new set attaches again with its new nranks / ranks — sl_peer_export yields the same
+ * handle as before.  A joiner first takes the group's state: sl_set_state with any member's sl_get_model (the
+ * models are bit-identical on all members) and, to continue the same minibatch schedule, option "step".  Detach
+ * wipes this replica's inbox; a symmetric buffer belongs to the caller, who zero-fills it before attaching it
+ * again.  Replicas that trained alone before they attach need no preparation. */
+int sl_peer_detach(sl_handle* h);
 int sl_comm_unique_id(void* id128);
 int sl_comm_init_rank(sl_handle* h, int nranks, int rank, const void* id128);
 int sl_allreduce_avg(sl_handle* h);

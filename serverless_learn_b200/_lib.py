@@ -45,6 +45,7 @@ _SIGS = {
     "sl_gossip_p2p_remote": (C.c_int, [_h, C.c_int]),
     "sl_peer_export": (C.c_int, [_h, C.c_void_p]),
     "sl_peer_attach": (C.c_int, [_h, C.c_int, C.c_int, C.c_void_p]),
+    "sl_peer_detach": (C.c_int, [_h]),
     "sl_peer_attach_symmetric": (C.c_int, [_h, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.c_void_p, C.c_size_t]),
     "sl_comm_unique_id": (C.c_int, [C.c_void_p]),
     "sl_comm_init_rank": (C.c_int, [_h, C.c_int, C.c_int, C.c_void_p]),

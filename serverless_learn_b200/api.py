@@ -249,6 +249,10 @@ class Replica:
         buf = C.create_string_buffer(handles, 64 * nranks) if handles else None
         self._ck(self._L.sl_peer_attach(self._h, nranks, rank, buf))
 
+    def peer_detach(self):
+        """Leave the synchronous group (every member does before a group of another size attaches)."""
+        self._ck(self._L.sl_peer_detach(self._h))
+
     def peer_attach_symmetric(self, nranks: int, rank: int, ptrs, multicast_ptr: int, nbytes: int):
         """Symmetric allocation made by the caller (e.g. torch.distributed._symmetric_memory): ptrs[p] = rank p's
         buffer as mapped here, multicast_ptr = its multicast address or 0."""

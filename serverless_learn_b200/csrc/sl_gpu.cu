@@ -239,6 +239,7 @@ struct sl_handle {
     int cl_scratch_F = 0;
     bool cl_dirty = false;               // a launch aborted: the accumulators are re-zeroed before the next one
     long long cl_xstep = 0;              // steps taken through K1c so far (accumulator parity continues across launches)
+    long long cl_gstep = 0;              // ... of them together with the attached group (cross-GPU buffer and tag)
     int cl_max_clusters[16] = {};        // per variant, for the shared-memory size in cl_smem_set
     size_t cl_smem_set[16] = {};
     int cl_coop = -1;                    // cooperative + cluster launch accepted? (-1 = not tried)
@@ -867,6 +868,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         a.lbase = a.lacc + 4;
         a.loss_out = loss_dev ? loss_dev + done : nullptr;
         a.xstep0 = h->cl_xstep;
+        a.gstep0 = h->cl_gstep;
         a.err = h->d_err;
         for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; }
         if (fused) {
@@ -885,6 +887,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
             h->k1_launches++;
             h->step += n;
             h->cl_xstep += n;
+            if (fused) h->cl_gstep += n;
             done += n;
             continue;
         }
@@ -926,6 +929,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         h->k1_launches++;
         h->step += n;
         h->cl_xstep += n;
+        if (fused) h->cl_gstep += n;
         done += n;
     }
     if (!in_graph) CK(h, cudaEventRecord(h->ev1, h->stream));
@@ -1963,6 +1967,7 @@ int sl_peer_attach(sl_handle* h, int nranks, int rank, const void* handles) {
     h->peer_n = nranks;
     h->peer_rank = rank;
     h->xflag_base = 0;
+    h->cl_gstep = 0;
     h->ipc_attached = true;
     if (h->nranks == 1) { h->nranks = nranks; h->rank = rank; }
     return SL_OK;
@@ -1986,7 +1991,34 @@ int sl_peer_attach_symmetric(sl_handle* h, int nranks, int rank, const void* con
     h->sym_n = nranks;
     h->peer_n = nranks;
     h->peer_rank = rank;
+    h->cl_gstep = 0;
     if (h->nranks == 1) { h->nranks = nranks; h->rank = rank; }
+    return SL_OK;
+}
+
+// Leave the group (every member does, before a group of another size is formed: a worker joined or died,
+// src/master.cc:79-91 / :177-196).  Unmaps the peers, forgets a symmetric buffer and wipes the own inbox so that
+// the next group starts from step tags and flags of zero.
+int sl_peer_detach(sl_handle* h) {
+    if (!h) return SL_EINVAL;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->peer_n) return SL_OK;
+    DeviceGuard dg(h->device);
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (h->ipc_attached)
+        for (int p = 0; p < h->peer_n; ++p)
+            if (p != h->peer_rank && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
+    for (int p = 0; p < 8; ++p) { h->peer_base[p] = nullptr; h->sym_buf[p] = nullptr; }
+    h->ipc_attached = false;
+    h->mc_gx = nullptr;
+    h->sym_n = 0;
+    h->peer_n = 0;
+    h->peer_rank = 0;
+    h->xflag_base = 0;
+    h->cl_gstep = 0;
+    if (!h->comm) { h->nranks = 1; h->rank = 0; }
+    if (h->xblock) CK(h, cudaMemset(h->xblock, 0, h->xblock_bytes));
+    CK(h, cudaDeviceSynchronize());
     return SL_OK;
 }
 

@@ -21,15 +21,15 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run(world, env_extra):
+def _run(world, env_extra, script="mgpu_sync_check.py", expect="model bit-identical on all ranks: True"):
     env = dict(os.environ, SL_BIG=str(1 << 16), **env_extra)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
-           os.path.join(ROOT, "tests", "mgpu_sync_check.py")]
+           os.path.join(ROOT, "tests", script)]
     p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
     out = p.stdout + p.stderr
     assert p.returncode == 0, out[-3000:]
-    assert "model bit-identical on all ranks: True" in out, out[-3000:]
+    assert expect in out, out[-3000:]
     return out
 
 
@@ -42,3 +42,12 @@ def test_sync_training_across_gpus_matches_the_oracle(F, B):
     world = 2 if n < 4 else 4
     out = _run(world, {"SL_F": str(F), "SL_B": str(B)})
     assert f"world={world}" in out
+
+
+@pytest.mark.parametrize("F,B", [(1024, 4096), (4096, 512)])
+def test_worker_joins_and_leaves_the_sync_group(F, B):
+    # alone -> join (state + step handed over) -> together -> detach -> alone -> attach again -> together
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least two GPUs")
+    _run(2, {"SL_F": str(F), "SL_B": str(B)}, script="mgpu_join_check.py", expect="join check passed")
