@@ -128,9 +128,11 @@ int sl_shard_synth(sl_handle* h, long long n_rows, unsigned long long row0,
  * continuing from the previous call (reset by sl_shard_end).  loss_out (nullable)
  * receives n_steps mean losses.  Blocks until the steps are done.
  * Range: gradient sums travel as 64-bit fixed point (units of 2^-32 with 7 count bits in the cluster
- * kernel, 2^-36 in the older kernels), so for every column |sum over the minibatch (and over all ranks)
- * of (sigmoid(z)-y)*x| must stay below about 1e5 (cluster kernel: 2^24 / (clusters * ranks) per cluster;
- * older kernels: 2^27 overall) — any fp32 data of ordinary scale; labels may be anywhere in [0,1].
+ * kernel, 2^-36 in the older kernels), so for every column |sum of (sigmoid(z)-y)*x| is bounded: in the
+ * cluster kernel each cluster's share of a minibatch (B / clusters rows, 33 clusters on a B200) must stay
+ * below 2^24 / (clusters * ranks) — 5.1e5 on one GPU, 6.4e4 with 8 ranks, i.e. features up to several
+ * hundred in magnitude at B = 4096; in the older kernels the whole minibatch's sum over all ranks below
+ * 2^27.  Any fp32 data of ordinary scale; labels may be anywhere in [0,1].
  * A partial sum outside the range (or not finite) fails the call with SL_EINVAL instead of wrapping:
  * the model is then not usable and should be restored (sl_set_state). */
 int sl_train_tick(sl_handle* h);
