@@ -50,9 +50,8 @@ struct ClArgs {
     unsigned long long* lacc;    // [3]    loss accumulators, same encoding, by step mod 3
     unsigned long long* lbase;   // [3]
     double* loss_out;      // device [n_steps]: mean loss of every step, written by the kernel; or nullptr
-    long long xstep0;      // accumulator parity of this launch's first step (continues across launches)
-    long long gstep0;      // steps the GROUP has taken together since it was attached: buffer and tag of the cross-GPU
-                           // words (a rank that trained alone before joining has another xstep0 than its peers)
+    long long xstep0;      // accumulator parity of this launch's first step (continues across launches); with peers
+                           // attached also buffer and tag of the cross-GPU words: the host keeps it equal on all ranks
     // same-box data parallel: one kernel per GPU, totals summed through peer-mapped memory
     int nranks, rank;      // nranks == 0: single GPU, no cross-GPU stage (1: the stage runs against itself)
     unsigned long long* peer_gx[8];  // rank p's all-rank words [2 buffers][F][8 ranks] as mapped here (own = local)
@@ -496,20 +495,19 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 // else one store per peer over NVLink); every rank then reads the slots of all ranks in its own
                 // memory and adds them up — integers again, the same bits everywhere.  A slot's previous content
                 // is two steps older (or the zero it started with) and never carries the current tag.
-                const unsigned long long tag = (unsigned long long)((a.gstep0 + s + 1) & 127);
-                const int bx = (int)((a.gstep0 + s) & 1);
+                const unsigned long long tag = (unsigned long long)((a.xstep0 + s + 1) & 127);
 #pragma unroll
                 for (int i = 0; i < XC; ++i) {
                     if (!xsend[i]) continue;
                     const unsigned long long word = ((unsigned long long)T[i] << 7) | tag;
-                    const size_t off = ((size_t)bx * F + col[i]) * 8 + a.rank;  // [buffer][column][rank]: a column's eight words share 64 bytes
+                    const size_t off = ((size_t)b * F + col[i]) * 8 + a.rank;  // [buffer][column][rank]: a column's eight words share 64 bytes
                     if (a.mc_gx) {
                         multimem_st_u64(a.mc_gx + off, word);
                     } else {
                         for (int p = 0; p < a.nranks; ++p) st_relaxed_sys_u64(a.peer_gx[p] + off, word);
                     }
                 }
-                const unsigned long long* mine = a.peer_gx[a.rank] + (size_t)bx * F * 8;
+                const unsigned long long* mine = a.peer_gx[a.rank] + (size_t)b * F * 8;
                 unsigned pend[XC];
                 long long S[XC];
 #pragma unroll

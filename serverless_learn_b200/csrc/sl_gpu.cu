@@ -831,6 +831,13 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         h->cl_scratch_F = F;
         h->cl_dirty = true;
     }
+    if (fused && h->cl_xstep != h->cl_gstep) {
+        // this replica has taken steps its peers have not (alone before it joined, or between two synchronous
+        // calls): its accumulators start afresh at the group's count — buffer and tag of the cross-GPU words
+        // follow xstep0, which must agree on all ranks
+        h->cl_xstep = h->cl_gstep;
+        h->cl_dirty = true;
+    }
     if (h->cl_dirty) {  // first use, or a launch gave up half way: start from zero (rare; costs a memset)
         CK(h, cudaMemsetAsync(h->cl_scratch, 0, 8 * words, h->stream));
         h->cl_dirty = false;
@@ -868,7 +875,6 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         a.lbase = a.lacc + 4;
         a.loss_out = loss_dev ? loss_dev + done : nullptr;
         a.xstep0 = h->cl_xstep;
-        a.gstep0 = h->cl_gstep;
         a.err = h->d_err;
         for (int k = 0; k < 8; ++k) { a.vX[k] = h->vX[k]; a.vy[k] = h->vy[k]; }
         if (fused) {

@@ -76,6 +76,8 @@ for mode in ("fused", "fused_mc", "nccl"):
             continue
     else:
         r.set_option("sync_path", 1)
+    for kv in filter(None, os.environ.get("SL_OPTS", "").split(",")):   # e.g. SL_OPTS=wait_all_owners=1
+        r.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     for key in ("xpoll_delay", "xpoll_gap", "poll_delay", "poll_gap"):
         if os.environ.get("SL_" + key.upper()):
             r.set_option(key, int(os.environ["SL_" + key.upper()]))
