@@ -436,14 +436,16 @@ def run_b200(args, rank, world, local_rank):
                   "variant": reps[0].info("variant"),
                   "hbm_gbs": (W2 * 4 * (F + 1) * B + 16 * F) * steps2 / c2_s / 1e9}
             # the same four workers in the reference's own structure: local steps only (gossip couples
-            # them every few seconds), all four side by side in one kernel, a quarter of the SMs each
+            # them every few seconds), all four side by side, a quarter of the clusters each
             Replica.train_steps_multi(reps, 64, want_loss=True)
             torch.cuda.synchronize()
             Replica.train_steps_multi(reps, steps2, want_loss=True)
             m_s = reps[0].last_train_ms() * 1e-3
             c2["local_steps"] = {"value": W2 * B * steps2 / m_s, "unit": UNIT, "ms_per_step": 1e3 * m_s / steps2,
-                                 "what": f"{W2} independent replicas, {steps2} local steps each, one kernel "
-                                         "(sl_train_steps_multi)"}
+                                 "what": f"{W2} independent replicas, {steps2} local steps each, side by side "
+                                         "(sl_train_steps_multi: one cluster-kernel launch per replica, a "
+                                         "quarter of the clusters each)",
+                                 "kernel_path": reps[0].info("path")}
             for rp in reps:
                 rp.close()
             import oracle

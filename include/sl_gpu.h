@@ -240,14 +240,16 @@ int sl_train_steps_sync(sl_handle* h, int n_steps, double* loss_out);
 int sl_train_steps_group(sl_handle* const* handles, int W, int n_steps, double* loss_out);
 /* W worker replicas that share one GPU each take n_steps LOCAL steps — the reference's own structure
  * (every worker process runs its own training thread, src/worker.cc:221-231,246, and only gossip
- * couples them): independent models, nothing summed across workers.  One persistent kernel.  For
- * W <= 4 and F <= 1024 the replicas are interleaved on every SM (the exchange of one model's step
- * hides behind the compute of the others; every worker ends bit-identical to sl_train_steps on its
- * own at F = 1024, within fp32 rounding of it for narrower rows, which the solo kernel groups
- * differently); otherwise the SMs are cut into W equal partitions (W <= 8, F <= 2048; every worker ends
- * bit-identical to sl_train_steps on its own with "grid" = SMs / W).  Same requirements as
- * sl_train_steps_group.  loss_out (nullable): W * n_steps doubles, worker-major.  No reference
- * counterpart. */
+ * couples them): independent models, nothing summed across workers.  Rows the cluster kernel takes (F a
+ * multiple of 16 up to 1024) run as W concurrent launches of it, one per replica on the replica's own stream
+ * with 1/W of the clusters each — every worker ends bit-identical to sl_train_steps on its own with option
+ * "clusters" set to that share; while one replica's step is in its exchange the others keep the row stream
+ * going.  Otherwise (or with option "path" = 1 on the first handle) ONE persistent kernel: for W <= 4 and
+ * F <= 1024 the replicas interleaved on every SM (every worker bit-identical to sl_train_steps on the older
+ * kernel at F = 1024, within fp32 rounding of it for narrower rows), else the SMs cut into W equal partitions
+ * (W <= 8, F <= 2048; bit-identical to sl_train_steps with "grid" = SMs / W).  Same requirements as
+ * sl_train_steps_group.  loss_out (nullable): W * n_steps doubles, worker-major.  sl_last_train_ms of the first
+ * handle: from the first launch to the last replica's end.  No reference counterpart. */
 int sl_train_steps_multi(sl_handle* const* handles, int W, int n_steps, double* loss_out);
 
 /* ---- allocation-free step ------------------------------------------------------------

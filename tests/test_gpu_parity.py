@@ -678,10 +678,11 @@ def test_multi_replicas_on_one_gpu_take_local_steps(sl, orc, W, n, F, B, variant
             r.load_shard(X, y)
         reps[0].set_option("variant", variant)
         lg = np.concatenate([sl.Replica.train_steps_multi(reps, 4), sl.Replica.train_steps_multi(reps, steps - 4)], axis=1)
-        # W <= 4 and F <= 1024 run interleaved on every SM (path 5: the full grid per replica), otherwise the
-        # SMs are cut into W partitions (path 1)
+        # rows the cluster kernel takes (F a multiple of 16 up to 1024, no explicit variant) run as W concurrent
+        # launches of it, each with 1/W of the clusters (path 8); otherwise W <= 4 and F <= 1024 run interleaved on
+        # every SM (path 5: the full grid per replica) and the rest with the SMs cut into W partitions (path 1)
         path = reps[0].info("path")
-        assert path in (1, 5)
+        assert path == (8 if variant == 0 and F % 16 == 0 and F <= 1024 else path) and path in (1, 5, 8)
         grid = reps[0].info("grid") // (W if path == 1 else 1)
         assert grid >= 1
         for k, r in enumerate(reps):
@@ -691,14 +692,45 @@ def test_multi_replicas_on_one_gpu_take_local_steps(sl, orc, W, n, F, B, variant
             assert r.info("step") == steps
             with sl.Replica(F, B, eta=eta) as solo:
                 solo.load_shard(*shards[k])
-                solo.set_option("variant", variant)
-                solo.set_option("grid", grid)
-                solo.set_option("path", 1)
+                if path == 8:    # the very launch sl_train_steps makes with "clusters" set to the replica's share
+                    cs = 8 if r.info("variant") - 100 in (1, 2, 3, 4, 12, 14, 16) else 4
+                    solo.set_option("path", 6)
+                    solo.set_option("clusters", r.info("grid") // cs)
+                else:
+                    solo.set_option("variant", variant)
+                    solo.set_option("grid", grid)
+                    solo.set_option("path", 1)
                 ls = solo.train_steps(steps)
-                if path == 1 or F == 1024:      # same arithmetic as the solo kernel: bit for bit
+                if path in (1, 8) or F == 1024:  # same arithmetic as the solo kernel: bit for bit
                     assert np.array_equal(solo.model(), r.model()) and np.array_equal(ls, lg[k]), k
                 else:                           # narrower rows: the solo kernel groups rows differently
                     assert w_err(solo.model(), r.model()) <= W_TOL
+    finally:
+        for r in reps:
+            r.close()
+
+
+def test_multi_replicas_after_solo_training_and_on_the_older_kernels(sl, orc):
+    # replicas that trained alone first (full-size launch, graph instantiated for 33 clusters) then side by side,
+    # then alone again; and "path" = 1 keeps the job on the older interleaved kernel
+    W, n, F, B, eta = 4, 3000, 1024, 512, 0.2
+    shards = [orc.synth(k * n, n, F) for k in range(W)]
+    reps = [sl.Replica(F, B, eta=eta) for _ in range(W)]
+    try:
+        refs = [np.zeros(F) for _ in range(W)]
+        for r, (X, y) in zip(reps, shards):
+            r.load_shard(X, y)
+            r.train_steps(3)
+        sl.Replica.train_steps_multi(reps, 5)
+        assert reps[0].info("path") == 8
+        for r in reps:
+            r.train_steps(2)
+        reps[0].set_option("path", 1)
+        sl.Replica.train_steps_multi(reps, 4)
+        assert reps[0].info("path") == 5
+        for k, r in enumerate(reps):
+            orc.lr_steps(*shards[k], B, 0, 14, refs[k], eta)
+            assert w_err(r.model(), refs[k]) <= W_TOL and r.info("step") == 14, k
     finally:
         for r in reps:
             r.close()
