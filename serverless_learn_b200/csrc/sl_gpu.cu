@@ -685,7 +685,7 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
         vi = (int)h->opt_cl_variant - 1;
         if (!fits(kClVariants[vi])) { *why = "requested cluster variant does not hold this F"; return false; }
     } else {
-        // measured at config 3 (tools/k1c_bench.py, profiles/r2_k1c.md): clusters of 4 put 132 of the 148 SMs to
+        // measured at config 3 (tools/k1c_bench.py, profiles/r2_k1c_timeline.md): clusters of 4 put 132 of the 148 SMs to
         // work (clusters of 8 only tile 120), and 16 compute warps take a CTA's 32 rows of a step in one pass.
         // Variant 15 (row copies issued by an exchange warp, 20 warps) measures within a few percent of 5 either
         // way from box to box; 5 also serves shapes with several passes per step.
