@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -232,7 +233,7 @@ struct sl_handle {
     struct RemoteState { double* model = nullptr; double* old = nullptr; double lambda = 0; bool used = false; };
     RemoteState remote[kMaxRemoteStates];
     std::thread::id lent_by;             // thread that holds mu between sl_state_lend and sl_state_reclaim
-    bool lent = false;
+    std::atomic<bool> lent{false};
     long long opt_sync_path = 0;         // 0 auto (fused when attached), 1 NCCL per step
     // cluster kernel (K1c)
     unsigned long long* cl_scratch = nullptr;  // [gacc 2F][gbase 2F][lacc 3 + pad][lbase 3 + pad]
@@ -1986,16 +1987,16 @@ int sl_state_lend(sl_handle* h) {
         h->mu.unlock();
         return SL_ECUDA;
     }
-    h->lent = true;
     h->lent_by = std::this_thread::get_id();
+    h->lent.store(true, std::memory_order_release);
     return SL_OK;
 }
 
 int sl_state_reclaim(sl_handle* h) {
     if (!h) return SL_EINVAL;
     // only the lending thread can get here with lent == true and be the owner of mu
-    if (!h->lent || h->lent_by != std::this_thread::get_id()) return SL_ESTATE;
-    h->lent = false;
+    if (!h->lent.load(std::memory_order_acquire) || h->lent_by != std::this_thread::get_id()) return SL_ESTATE;
+    h->lent.store(false, std::memory_order_relaxed);
     h->mu.unlock();
     return SL_OK;
 }
