@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     static_assert(CREG == 0 || (WPG * RG) % 4 == 0, "register re-split needs whole compute warpgroups");
     constexpr int NCW = WPG * RG;     // compute warps
     constexpr int XT = XW * 32;       // exchange threads
-    constexpr int XC = (1024 / CS + XT - 1) / XT;  // owned columns per exchange thread (F <= 1024)
+    constexpr int XC = (128 * WPG / CS + XT - 1) / XT;  // owned columns per exchange thread (F <= 128 * WPG)
     constexpr int SPB = R / RS;       // ring slots per pass
     constexpr int NSRC = CS * RG;     // gradient partials an owner receives per step
     constexpr int CT = WPG * 32;      // threads of a row group

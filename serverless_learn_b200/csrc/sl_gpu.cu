@@ -151,6 +151,8 @@ const ClVariant kClVariants[] = {
     SL_CLUSTER(8, 2, 16, 8, 8, 2, 104, 64),  // 14: as 1 with 8-row slots
     SL_CLUSTER_P(8, 2, 16, 8, 4, 4, 104, 64, 0),  // 15: as 5 with four exchange warps, one of which also issues the row copies
     SL_CLUSTER_P(8, 2, 16, 8, 8, 4, 104, 64, 0),  // 16: the same in clusters of 8
+    SL_CLUSTER(16, 1, 16, 4, 4, 3, 104, 64),      // 17: F <= 2048: one row group of 16 warps, 16 rows per pass
+    SL_CLUSTER(16, 1, 16, 4, 4, 4, 0, 0),         // 18: the same without the register re-split, four exchange warps
 };
 constexpr int kNumClVariants = sizeof(kClVariants) / sizeof(kClVariants[0]);
 
@@ -241,8 +243,8 @@ struct sl_handle {
     bool cl_dirty = false;               // a launch aborted: the accumulators are re-zeroed before the next one
     long long cl_xstep = 0;              // steps taken through K1c so far (accumulator parity continues across launches)
     long long cl_gstep = 0;              // ... of them together with the attached group (cross-GPU buffer and tag)
-    int cl_max_clusters[16] = {};        // per variant, for the shared-memory size in cl_smem_set
-    size_t cl_smem_set[16] = {};
+    int cl_max_clusters[32] = {};        // per variant, for the shared-memory size in cl_smem_set
+    size_t cl_smem_set[32] = {};
     int cl_coop = -1;                    // cooperative + cluster launch accepted? (-1 = not tried)
     // [record ev0] -> [kernel] -> [record ev1] as one instantiated graph: the three reach the GPU together, so
     // the device does not sit between the first time stamp and the kernel waiting for the host's launch call
@@ -680,6 +682,7 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
     const int F = h->F;
     if (h->npart > 1) { *why = "independent replicas run on the interleaved kernel"; return false; }
     if (((uintptr_t)(h->shard + h->shard_off) & 15) != 0) { *why = "shard not 16-byte aligned"; return false; }
+    if (fused && F > 1024) { *why = "rows wider than 1024 floats exchange across GPUs in the older kernels"; return false; }
     int vi = -1;
     auto fits = [&](const ClVariant& v) { return F % (4 * v.cs) == 0 && F <= 128 * v.wpg; };
     if (h->opt_cl_variant > 0 && h->opt_cl_variant <= kNumClVariants) {
@@ -696,7 +699,15 @@ bool plan_cluster(sl_handle* h, ClusterPlan* p, std::string* why, bool fused) {
             for (int k = 0; k < kNumClVariants; ++k)
                 if (fits(kClVariants[k]) && cluster_capacity(h, k) >= 1) { vi = k; break; }
         }
-        if (vi < 0) { *why = "F must be a multiple of 32 and at most 1024 for the cluster kernel"; return false; }
+        if (vi < 0) { *why = "F must be a multiple of 16 and at most 2048 for the cluster kernel"; return false; }
+        // rows wider than 1024 floats (variant 17: 16 rows per pass): measured ahead of the older kernel up to three
+        // passes per step (F = 2048: 8.5 against 10.7 us at B = 4096), behind it from four on (15.5 against 15.0 at 8192)
+        if (F > 1024 && h->opt_path == 0) {
+            const long long Bq = (long long)h->B * (h->vw > 1 ? h->vw : 1);
+            const long long per_cta = (Bq + (long long)cluster_capacity(h, vi) * kClVariants[vi].cs - 1) /
+                                      ((long long)cluster_capacity(h, vi) * kClVariants[vi].cs);
+            if (per_cta > 48) { *why = "wide rows with more than three passes per step run on the older kernel"; return false; }
+        }
     }
     const ClVariant& v = kClVariants[vi];
     int ncl = cluster_capacity(h, vi);
@@ -1645,6 +1656,10 @@ static int run_multi_cluster(sl_handle* const* hs, int W, int n_steps, double* l
     *ran = false;
     sl_handle* h0 = hs[0];
     if (!(h0->opt_path == 0 || h0->opt_path == 6) || h0->opt_variant != 0) return SL_OK;
+    if (h0->F > 1024) {   // wider rows: a replica's share of the clusters would take four and more passes per step
+        if (h0->opt_path == 6) return fail(h0, SL_EINVAL, "cluster kernel requested but sl_train_steps_multi uses it up to F = 1024");
+        return SL_OK;
+    }
     std::vector<ClusterPlan> plans((size_t)W);
     std::string why;
     for (int k = 0; k < W; ++k) {

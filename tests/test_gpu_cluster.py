@@ -47,20 +47,39 @@ SHAPES = [
     (9000, 1024, 4096),   # config-3 minibatch: 32 rows per CTA
     (5000, 992, 1111),    # F a multiple of 32 below the maximum, B not a multiple of anything
     (40000, 1024, 16384),  # several passes per row group and step
+    (3000, 2048, 600),    # rows wider than 1024 floats: the 16-warp row group (variants 17, 18)
+    (5000, 1536, 4096),
 ]
 
 
-@pytest.mark.parametrize("clv", list(range(1, 17)))
+@pytest.mark.parametrize("clv", list(range(1, 19)))
 @pytest.mark.parametrize("shape", SHAPES)
 def test_cluster_kernel_matches_the_oracle(sl, orc, clv, shape):
     n, F, B = shape
-    if clv == 4 and F > 512:
+    if (clv == 4 and F > 512) or (clv <= 16 and F > 1024):
         with pytest.raises(sl.SlError):
             _run(sl, orc, 64, F, 16, 1, 0.2, clv=clv)
         return
     ew, el, info, _, _ = _run(sl, orc, n, F, B, 7, 0.2, clv=clv)
     assert info[0] == 6 and info[1] == 100 + clv
     assert ew <= W_TOL and el <= L_TOL, (ew, el, info)
+
+
+@pytest.mark.parametrize("F,B,want_path", [(2048, 600, 6), (1536, 4096, 6), (2048, 8192, 1)])
+def test_wide_rows_choose_their_kernel(sl, orc, F, B, want_path):
+    # nothing forced: rows of 1025..2048 floats take the cluster kernel's 16-warp row group up to three passes per
+    # step and the older persistent kernel beyond; either way the oracle's numbers
+    n, steps, eta = 2 * B + 100, 5, 0.2
+    X, y = orc.synth(0, n, F)
+    w = np.zeros(F)
+    lo = orc.lr_steps(X, y, B, 0, steps, w, eta)
+    with sl.Replica(F, B, eta=eta) as r:
+        r.load_shard(X, y)
+        lg = r.train_steps(steps)
+        assert r.info("path") == want_path, (r.info("path"), r.info("variant"))
+        if want_path == 6:
+            assert r.info("variant") == 117
+        assert w_err(r.model(), w) <= W_TOL and float(np.max(np.abs(lg - lo) / lo)) <= L_TOL
 
 
 @pytest.mark.parametrize("clusters", [1, 2, 5, 0])
