@@ -653,13 +653,23 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 // one barrier per owner CTA: a warp starts on its columns as soon as THEIR owner's weights are here
                 // (the owners finish their L2 hop up to half a microsecond apart); the thread that holds an owner's
                 // first columns re-arms that barrier
-                if (gv) {
-                    if (a.wait_all_owners)   // comparison switch: behave as one barrier for all weights
-                        for (int o = 0; o < CS; ++o) mbar_wait_cluster(smem_u32(&wfull[o]), (uint32_t)(s - 1) & 1u, a.err);
-                    mbar_wait_cluster(smem_u32(&wfull[owner]), (uint32_t)(s - 1) & 1u, a.err);
-                    if (rg == 0 && gq * 4 == owner * fc && s + 1 < n_steps)
-                        mbar_arrive_expect_tx(smem_u32(&wfull[owner]), (uint32_t)fc * 4u);
+                if ((fc & 127) == 0) {
+                    // no warp's 128 columns span two owners (F = 1024 in clusters of 4 or 8): every lane waits for its own
+                    if (gv) {
+                        if (a.wait_all_owners)   // comparison switch: behave as one barrier for all weights
+                            for (int o = 0; o < CS; ++o) mbar_wait_cluster(smem_u32(&wfull[o]), (uint32_t)(s - 1) & 1u, a.err);
+                        mbar_wait_cluster(smem_u32(&wfull[owner]), (uint32_t)(s - 1) & 1u, a.err);
+                    }
+                } else {
+                    // warp-uniform: a warp whose columns span several owners waits for one after the other (lanes spinning
+                    // on different barriers would take turns: F = 992 measured 5.5 us/step that way, 4.0 this way)
+                    const int wo_lo = (wig * 128) / fc, wo_hi = wig * 128 < F ? (min(F, wig * 128 + 128) - 1) / fc : -1;
+                    const int lo_o = a.wait_all_owners ? 0 : wo_lo, hi_o = a.wait_all_owners ? CS - 1 : wo_hi;
+                    if (wo_lo <= wo_hi)
+                        for (int o = lo_o; o <= hi_o; ++o) mbar_wait_cluster(smem_u32(&wfull[o]), (uint32_t)(s - 1) & 1u, a.err);
                 }
+                if (gv && rg == 0 && gq * 4 == owner * fc && s + 1 < n_steps)
+                    mbar_arrive_expect_tx(smem_u32(&wfull[owner]), (uint32_t)fc * 4u);
                 if (gv) w = lds_v4(wsm_a + (uint32_t)((s & 1) * F + gq * 4) * 4u);
             };
             if (nsb == 0 && s > 0) take_weights();  // a CTA without rows still takes part in every exchange
