@@ -181,7 +181,11 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 #ifndef SL_CL_FINE_STAMPS
 #define SL_CL_FINE_STAMPS 0
 #endif
+// Compiled in only in the DBG instantiation of the kernel (option debug_timeline): the stamps' pointer and step
+// compares otherwise cost the compute warps registers they do not have (3.82 -> 3.68 us/step at config 3).
+template <bool DBG>
 __device__ __forceinline__ void cl_stamp(const ClArgs& a, int s, int point) {
+    if (!DBG) return;
     if (a.dbg != nullptr && s >= a.dbg_step && s < a.dbg_step + 4) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -264,7 +268,7 @@ __device__ __forceinline__ void poll_totals(unsigned long long* const (&p)[XC], 
 // registers per thread from the exchange / producer warps (setmaxnreg), which keep XREG.  PW = 1: a warp of
 // its own issues the TMA row copies; PW = 0: lanes of the first exchange warp do, once per step after the
 // weights have gone out (for shapes where a step is one pass: a slot is then always free when it is asked for).
-template <int WPG, int RG, int R, int RS, int CS, int XW, int CREG, int XREG, int PW>
+template <int WPG, int RG, int R, int RS, int CS, int XW, int CREG, int XREG, int PW, bool DBG>
 __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_cluster_kernel(const ClArgs a) {
     static_assert(R % RS == 0, "a pass is a whole number of ring slots");
     static_assert(WPG > 1, "the labels become visible at the row group's barrier");
@@ -315,7 +319,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     const uint32_t recv_bytes = (uint32_t)NSRC * (uint32_t)fc * 4u;
 
     if (tid == 0) {
-        if (!SL_CL_FINE_STAMPS) cl_stamp(a, a.dbg_step, 14);  // kernel entry
+        if (!SL_CL_FINE_STAMPS) cl_stamp<DBG>(a, a.dbg_step, 14);  // kernel entry
         for (int s = 0; s < RG * nsg; ++s) {
             mbar_init(smem_u32(&full[s]), 1);
             mbar_init(smem_u32(&empty[s]), WPG);
@@ -337,7 +341,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     }
     __syncthreads();
     cluster_sync_all();  // every CTA's barriers exist before anybody stores into a neighbour
-    if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp(a, a.dbg_step, 9);
+    if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp<DBG>(a, a.dbg_step, 9);
 
     // ---- TMA producer: lane l owns ring slot l % nsg of row group l / nsg and fetches that slot's uses over the
     // whole launch (issuing a slot costs a thread several hundred cycles; one lane would bound the step)
@@ -439,7 +443,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             }
             mbar_wait_cluster(smem_u32(rfull), (uint32_t)s & 1u, a.err);
             if (t == 0) {
-                cl_stamp(a, s, 6);
+                cl_stamp<DBG>(a, s, 6);
                 if (s + 1 < n_steps) mbar_arrive_expect_tx(smem_u32(rfull), recv_bytes);
             }
             // the cluster's sum of every owned column: all partials are read and converted before the first
@@ -482,12 +486,12 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(xdone));
             if (bad) set_err(a.err, kErrRange);
-            if (t == 0) cl_stamp(a, s, 7);
+            if (t == 0) cl_stamp<DBG>(a, s, 7);
             poll_totals<false, XC>(lp, lact, lpv, T, (unsigned)a.ncl, a.poll_delay, a.poll_gap, a.err, kErrTimeoutPart, kSpinLimit);
 #pragma unroll
             for (int i = 0; i < XC; ++i)
                 if (lact[i]) xprev[b * fc + t + i * XT] = lpv[i];
-            if (t == 0) cl_stamp(a, s, 3);
+            if (t == 0) cl_stamp<DBG>(a, s, 3);
             if (a.nranks > 0) {
                 // ---- across GPUs: one 8-byte word per (rank, column) and buffer, value in the upper 57 bits and a
                 // step tag in the lower 7: the thread that forwards a column stores this GPU's total into slot
@@ -555,7 +559,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 }
 #pragma unroll
                 for (int i = 0; i < XC; ++i) T[i] = S[i];
-                if (!SL_CL_FINE_STAMPS && t == 0) cl_stamp(a, s, 8);
+                if (!SL_CL_FINE_STAMPS && t == 0) cl_stamp<DBG>(a, s, 8);
             }
             // new fp32 weights to every CTA of the cluster, 16 bytes per store: the four lanes of a quad hold
             // four consecutive columns; each gathers the quad's values and serves a quarter of the CTAs
@@ -578,7 +582,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                     }
                 }
             }
-            if (t == 0) cl_stamp(a, s, 4);
+            if (t == 0) cl_stamp<DBG>(a, s, 4);
             if (!PW && warp == NCW) {
                 // refill the slots whose previous use is consumed by now: the rows of step s+1 went into registers
                 // right after this step's partials had been read
@@ -614,7 +618,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             const double* m = a.model + gq * 4;
             w = make_float4((float)m[0], (float)m[1], (float)m[2], (float)m[3]);
         }
-        if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp(a, a.dbg_step, 10);
+        if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp<DBG>(a, a.dbg_step, 10);
         // where this thread's gradient chunk goes: the owner CTA of its columns, one slot per (source CTA, group)
         const int owner = gv ? (gq * 4) / fc : 0;
         const uint32_t send_addr = mapa_u32(smem_u32(recv) + (uint32_t)((((int)crank * RG + rg) * fc + (gq * 4 - owner * fc)) * 4), (uint32_t)owner);
@@ -648,7 +652,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
             const long long mb_next = wrap(mb + a.vB);
             float2 glo = make_float2(0.f, 0.f), ghi = make_float2(0.f, 0.f);  // gradient of this thread's four columns
             float2* zyb = zy + (size_t)(s & 1) * a.zy_rows;
-            if (tid == 0) cl_stamp(a, s, 0);
+            if (tid == 0) cl_stamp<DBG>(a, s, 0);
             auto take_weights = [&]() {
                 // one barrier per owner CTA: a warp starts on its columns as soon as THEIR owner's weights are here
                 // (the owners finish their L2 hop up to half a microsecond apart); the thread that holds an owner's
@@ -683,7 +687,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 for (int qq = 0; qq < SPB; ++qq) {
                     if (qq * RS < rc) {  // warp-uniform
                         mbar_wait(smem_u32(&gfullb[slot]), par, a.err);
-                        if (!SL_CL_FINE_STAMPS && tid == 0 && s == 0 && sb == 0 && qq == 0) cl_stamp(a, a.dbg_step, 11);
+                        if (!SL_CL_FINE_STAMPS && tid == 0 && s == 0 && sb == 0 && qq == 0) cl_stamp<DBG>(a, a.dbg_step, 11);
                         const uint32_t sbase = smem_u32(gring + (size_t)slot * slot_bytes);
 #pragma unroll
                         for (int rr = 0; rr < RS; ++rr) {
@@ -699,11 +703,11 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                         for (int rr = 0; rr < RS; ++rr) x[qq * RS + rr] = make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                 }
-                if (SL_CL_FINE_STAMPS && tid == 0 && sb == 1) cl_stamp(a, s, 12);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb == 1) cl_stamp<DBG>(a, s, 12);
                 if (sb == 0 && s > 0) {
                     // the rows of the step's first pass are already in registers: only now wait for the weights
                     take_weights();
-                    if (tid == 0) cl_stamp(a, s, 5);
+                    if (tid == 0) cl_stamp<DBG>(a, s, 5);
                 }
                 // packed fp32 pairs (FFMA2): half the issue slots of the two inner loops
                 float d[R];
@@ -716,7 +720,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                 }
                 MultiReduce<R, 16>::run(d, lane);
                 float z = d[0];  // warp total for row ridx
-                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 8 : 13);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp<DBG>(a, s, sb == 0 ? 8 : 13);
                 if (WPG > 1) {
                     float* rb = red + red_buf * (NCW * R);
                     if (canon) rb[(rg * WPG + wig) * R + ridx] = z;
@@ -727,14 +731,14 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                     for (int k = 0; k < WPG; ++k) z += rb[(rg * WPG + k) * R + ridx];
                     red_buf ^= 1;
                 }
-                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 9 : 14);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp<DBG>(a, s, sb == 0 ? 9 : 14);
                 float resid = 0.f;
                 if (ridx < rc) {
                     const float yv = ybuf[(size_t)((s & 1) * RG + rg) * a.ycap + sb * R + ridx];
                     resid = __frcp_rn(1.0f + __expf(-z)) - yv;  // MUFU.EX2 / MUFU.RCP: ~2 ulp, far inside the tolerance
                     if (canon && wig == 0 && want_loss) zyb[j * R + ridx] = make_float2(z, yv);
                 }
-                if (SL_CL_FINE_STAMPS && tid == 0 && sb == 0) cl_stamp(a, s, 10);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb == 0) cl_stamp<DBG>(a, s, 10);
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     const float rr = __shfl_sync(0xffffffffu, resid, lane_of_row<R>(r));
@@ -742,12 +746,12 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
                     glo = __ffma2_rn(rr2, make_float2(x[r].x, x[r].y), glo);
                     ghi = __ffma2_rn(rr2, make_float2(x[r].z, x[r].w), ghi);
                 }
-                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp(a, s, sb == 0 ? 11 : 15);
+                if (SL_CL_FINE_STAMPS && tid == 0 && sb < 2) cl_stamp<DBG>(a, s, sb == 0 ? 11 : 15);
             }
-            if (tid == 0) cl_stamp(a, s, 1);
+            if (tid == 0) cl_stamp<DBG>(a, s, 1);
             // ---- hand the gradient chunk to the owner of its columns, straight from registers
             if (gv) st_async_v4(send_addr, make_float4(glo.x, glo.y, ghi.x, ghi.y), send_bar);
-            if (tid == 0) cl_stamp(a, s, 2);
+            if (tid == 0) cl_stamp<DBG>(a, s, 2);
             // ---- off the critical path: this group's loss of the step
             if (wig == 0 && want_loss) {
                 float l = 0.f;
@@ -806,7 +810,7 @@ __global__ void __launch_bounds__(cl_warps<WPG, RG, XW, CREG, PW>() * 32, 1) lr_
     // nobody leaves while a neighbour may still store into its shared memory
     __syncwarp();
     cluster_sync_all();
-    if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp(a, a.dbg_step, 15);  // kernel exit
+    if (!SL_CL_FINE_STAMPS && tid == 0) cl_stamp<DBG>(a, a.dbg_step, 15);  // kernel exit
 }
 
 }  // namespace slk

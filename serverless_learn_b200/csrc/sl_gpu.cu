@@ -128,10 +128,12 @@ constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 struct ClVariant {
     int wpg, rg, r, rs, cs, warps;
     const void* fn;
+    const void* fn_dbg;   // the same kernel with the timeline stamps compiled in (option debug_timeline)
 };
 #define SL_CLUSTER_P(WPG, RG, R, RS, CS, XW, CREG, XREG, PW) \
     ClVariant { WPG, RG, R, RS, CS, slk::cl_warps<WPG, RG, XW, CREG, PW>(), \
-                (const void*)slk::lr_cluster_kernel<WPG, RG, R, RS, CS, XW, CREG, XREG, PW> }
+                (const void*)slk::lr_cluster_kernel<WPG, RG, R, RS, CS, XW, CREG, XREG, PW, false>, \
+                (const void*)slk::lr_cluster_kernel<WPG, RG, R, RS, CS, XW, CREG, XREG, PW, true> }
 #define SL_CLUSTER(WPG, RG, R, RS, CS, XW, CREG, XREG) SL_CLUSTER_P(WPG, RG, R, RS, CS, XW, CREG, XREG, 1)
 const ClVariant kClVariants[] = {
     SL_CLUSTER(8, 2, 16, 4, 8, 2, 104, 64),  // 1: F <= 1024, two row groups of 16 rows: a CTA's 32 rows of config 3 in
@@ -648,13 +650,15 @@ int cluster_capacity(sl_handle* h, int vi) {
     const ClVariant& v = kClVariants[vi];
     h->cl_max_clusters[vi] = 0;
     h->cl_smem_set[vi] = h->smem_optin;
-    if (cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin) != cudaSuccess) {
-        cudaGetLastError();
-        return 0;
-    }
-    if (v.cs > 8 && cudaFuncSetAttribute(v.fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
-        cudaGetLastError();
-        return 0;
+    for (const void* fn : {v.fn, v.fn_dbg}) {
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin) != cudaSuccess) {
+            cudaGetLastError();
+            return 0;
+        }
+        if (v.cs > 8 && cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+            cudaGetLastError();
+            return 0;
+        }
     }
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
@@ -775,17 +779,18 @@ size_t xblock_bytes_for(int F) { return xblock_gx_offset(F) + xblock_gx_bytes(F)
 
 // One launch of the cluster kernel between ev0 and ev1 as an instantiated graph (see sl_handle::cl_graph).
 // Returns false when graphs cannot carry this launch here; the caller then launches directly.
-bool cluster_graph_launch(sl_handle* h, const ClusterPlan& plan, const ClVariant& v, slk::ClArgs* a) {
+bool cluster_graph_launch(sl_handle* h, const ClusterPlan& plan, const ClVariant& v, const void* kfn, slk::ClArgs* a) {
     if (h->cl_graph_ok == 0) return false;
     void* params[] = {a};
     cudaKernelNodeParams kp;
     memset(&kp, 0, sizeof(kp));
-    kp.func = const_cast<void*>(v.fn);
+    kp.func = const_cast<void*>(kfn);
+    const int gkey = plan.variant * 2 + (kfn == v.fn_dbg ? 1 : 0);
     kp.gridDim = dim3((unsigned)plan.grid);
     kp.blockDim = dim3((unsigned)plan.threads);
     kp.sharedMemBytes = (unsigned)plan.smem;
     kp.kernelParams = params;
-    const bool same = h->cl_gexec && h->cl_graph_variant == plan.variant && h->cl_graph_grid == plan.grid &&
+    const bool same = h->cl_gexec && h->cl_graph_variant == gkey && h->cl_graph_grid == plan.grid &&
                       h->cl_graph_threads == plan.threads && h->cl_graph_smem == plan.smem;
     auto give_up = [&]() {
         cudaGetLastError();
@@ -818,7 +823,7 @@ bool cluster_graph_launch(sl_handle* h, const ClusterPlan& plan, const ClVariant
         }
         if (cudaGraphAddEventRecordNode(&n2, h->cl_graph, &h->cl_gnode, 1, h->ev1) != cudaSuccess) return give_up();
         if (cudaGraphInstantiate(&h->cl_gexec, h->cl_graph, 0) != cudaSuccess) return give_up();
-        h->cl_graph_variant = plan.variant;
+        h->cl_graph_variant = gkey;
         h->cl_graph_grid = plan.grid;
         h->cl_graph_threads = plan.threads;
         h->cl_graph_smem = plan.smem;
@@ -868,6 +873,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         CK(h, cudaMemsetAsync(h->dbg, 0, dw * 8, h->stream));
         dbg = h->dbg;
     }
+    const void* kfn = dbg ? v.fn_dbg : v.fn;   // the timeline stamps exist only in the debug instantiation
     const bool one_graph = n_steps <= max_per_launch && !dbg && h->opt_cl_graph != 0;
     bool in_graph = false;
     if (!one_graph) CK(h, cudaEventRecord(h->ev0, h->stream));
@@ -899,7 +905,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         }
         a.dbg = done == 0 ? dbg : nullptr;
         a.dbg_step = done == 0 && dbg ? (int)h->opt_dbg_step : 0;
-        if (one_graph && cluster_graph_launch(h, plan, v, &a)) {
+        if (one_graph && cluster_graph_launch(h, plan, v, kfn, &a)) {
             in_graph = true;
             h->launches++;
             h->k1_launches++;
@@ -929,7 +935,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         cudaError_t e = cudaErrorUnknown;
         if (h->cl_coop != 0) {
             cfg.numAttrs = 2;
-            e = cudaLaunchKernelExC(&cfg, v.fn, params);
+            e = cudaLaunchKernelExC(&cfg, kfn, params);
             if (h->cl_coop < 0) {
                 h->cl_coop = e == cudaSuccess ? 1 : 0;
                 if (e != cudaSuccess) cudaGetLastError();
@@ -937,7 +943,7 @@ int run_cluster(sl_handle* h, const ClusterPlan& plan, int n_steps, double* loss
         }
         if (h->cl_coop == 0) {
             cfg.numAttrs = 1;
-            e = cudaLaunchKernelExC(&cfg, v.fn, params);
+            e = cudaLaunchKernelExC(&cfg, kfn, params);
         }
         if (e != cudaSuccess) {
             cudaGetLastError();
